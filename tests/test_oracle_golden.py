@@ -1,0 +1,142 @@
+"""Pin the numpy oracle to fixtures produced by the reference's own code
+(tests/golden/make_golden.py).  CPU only."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+from oracle import xeng_oracle as orc
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name), allow_pickle=False)
+
+
+@pytest.mark.parametrize("tag", ["random", "chanramp"])
+def test_corr_full_matches_reference_generator(golden_dir, tag):
+    g = _load(golden_dir, "golden_corr_%s.npz" % tag)
+    vin, acc = g["vin"], int(g["acc_len"])
+    for blk in range(vin.shape[0] // acc):
+        re, im = orc.corr_full(vin[blk * acc:(blk + 1) * acc])
+        assert np.array_equal(re, g["corr_re"][blk])
+        assert np.array_equal(im, g["corr_im"][blk])
+
+
+def test_regtile_index_matches_reference(golden_dir):
+    g = _load(golden_dir, "golden_regtile.npz")
+    for nstand in (4, 8, 12):
+        in0, in1, idx = orc.xgpu_maps(nstand)
+        assert np.array_equal(idx, g["regtile_%d" % nstand])
+    in0, in1, idx = orc.xgpu_maps(352)
+    assert np.array_equal(idx[::997], g["regtile_352_sample"])
+    assert idx.max() == int(g["regtile_352_max"])
+    dig = np.frombuffer(hashlib.sha256(idx.astype("<i8").tobytes()).digest(), dtype=np.uint8)
+    assert np.array_equal(dig, g["regtile_352_sha256"])
+    tri = np.array([[orc.tri_index(i, j) for j in range(8)] for i in range(8)])
+    assert np.array_equal(tri, g["tri"])
+
+
+def test_regtile_352_geometry():
+    """W = 249216 words/channel, 248512 used, 704 padding."""
+    in0, in1, idx = orc.xgpu_maps(352)
+    W = orc.words_per_chan(352)
+    assert W == 249216 and W * 192 == 47849472     # xgpu_test.py:9
+    assert idx.size == 248512 and np.unique(idx).size == idx.size
+    assert idx.min() == 0 and idx.max() < W
+
+
+def test_corr_xgpu_matches_Corr_test(golden_dir):
+    """Corr._test (reference numpy correlator) read through regtile_index, as
+    Corr._compare / xgpu_test.py do."""
+    g = _load(golden_dir, "golden_corr_test.npz")
+    vin = g["vin"]
+    nt, nchan, nstand, npol = vin.shape
+    x = orc.corr_xgpu(vin)
+    lit = orc.corr_loop_literal(vin)
+    assert np.array_equal(lit.real.astype(np.int32), g["out_re"])
+    assert np.array_equal(lit.imag.astype(np.int32), g["out_im"])
+    used = np.zeros(x.shape[2], dtype=bool)
+    for i0 in range(nstand):
+        for i1 in range(i0, nstand):
+            for p in range(4):
+                p0, p1 = p // 2, p % 2
+                k = orc.regtile_index(2 * i0 + p0, 2 * i1 + p1, nstand)
+                used[k] = True
+                assert np.array_equal(x[0, :, k], g["out_re"][:, i0, i1, p])
+                assert np.array_equal(x[1, :, k], g["out_im"][:, i0, i1, p])
+    assert not x[:, :, ~used].any()          # padding words stay zero
+    assert (~used).sum() == nstand // 2 * 4
+
+
+def test_get_order_subselect_reorder_conventions(golden_dir):
+    """bfXgpuGetOrder/SubSelect/Reorder net effect: v(s0,p0) conj(v(s1,p1)) in
+    any stand order (corr_output_full_block.py:582-591, test_corr_part_rx.py:76-84)."""
+    g = _load(golden_dir, "golden_corr_random.npz")
+    vin, acc = g["vin"], int(g["acc_len"])
+    v = vin[:acc]
+    nt, nchan, nstand, npol = v.shape
+    gold_re, gold_im = g["corr_re"][0], g["corr_im"][0]
+    x = orc.corr_xgpu(v)
+    a2i = np.arange(nstand * npol).reshape(nstand, npol)
+    a2bl, conj = orc.get_order(a2i)
+    ro = orc.reorder(x, a2bl, conj)
+    assert np.array_equal(ro[..., 0], np.moveaxis(gold_re, 0, -1))
+    assert np.array_equal(ro[..., 1], np.moveaxis(gold_im, 0, -1))
+    rng = np.random.default_rng(1)
+    bls = [[[int(a), int(b)], [int(c), int(d)]] for a, b, c, d in
+           zip(rng.integers(0, nstand, 50), rng.integers(0, 2, 50),
+               rng.integers(0, nstand, 50), rng.integers(0, 2, 50))]
+    vm, cj = orc.baselines_to_vismap(bls, a2bl, conj)
+    out = orc.subselect(x, vm, cj, nchan_sum=3)
+    for n, ((s0, p0), (s1, p1)) in enumerate(bls):
+        assert out[0, n, 0] == gold_re[:, s0, s1, p0, p1].sum()
+        assert out[0, n, 1] == gold_im[:, s0, s1, p0, p1].sum()
+
+
+def test_corr_accumulates_over_gulps(golden_dir):
+    g = _load(golden_dir, "golden_corr_random.npz")
+    vin = g["vin"]
+    whole = orc.corr_xgpu(vin)
+    acc = np.zeros(whole.shape, dtype=np.int64)
+    for k in range(0, vin.shape[0], 16):
+        orc.corr_xgpu(vin[k:k + 16], acc=acc)
+    assert np.array_equal(acc, whole)
+    a = np.zeros_like(whole)
+    orc.corr_acc(a, whole, first=True)
+    orc.corr_acc(a, whole, first=False)
+    assert np.array_equal(a, 2 * whole)
+
+
+def test_unpack_edge_bytes():
+    re, im = orc.unpack4(np.array([0xFF, 0x88, 0x80, 0x08, 0x78, 0x87, 0x00], dtype=np.uint8))
+    assert re.tolist() == [-1, -8, -8, 0, 7, -8, 0]
+    assert im.tolist() == [-1, -8, 0, -8, -8, 7, 0]
+
+
+def test_beamform_matches_reference(golden_dir):
+    g = _load(golden_dir, "golden_beamform.npz")
+    vin = g["vin"]
+    nt, nchan, nstand, npol = vin.shape
+    v = vin.reshape(nt, nchan, nstand * npol)
+    r, i = orc.unpack4(v)
+    assert np.array_equal((r + 1j * i).astype(np.complex64), g["unpacked"])
+    out = orc.beamform(v, g["coeffs"])
+    ref = g["out"]
+    assert np.allclose(out, ref, rtol=1e-4, atol=1e-4 * np.abs(ref).max())  # ref is complex64 sums
+    # weights built by the reference block from control JSON
+    freqs = float(g["chan_bw_hz"]) * np.arange(nchan)
+    for b in range(g["coeffs"].shape[1]):
+        w = orc.beam_weights(freqs, g["delays"][b], g["amps"][b], g["calgains"][:, b, :])
+        bg = g["block_gains"][:, b, :]
+        assert np.allclose(w, bg, rtol=1e-5, atol=1e-5 * np.abs(bg).max())
+        assert np.allclose(w, g["coeffs"][:, b, :], rtol=2e-4, atol=1e-3)
+
+
+def test_beam_power_sum_matches_reference(golden_dir):
+    g = _load(golden_dir, "golden_beamsum.npz")
+    out = orc.beam_power_sum(g["x"], int(g["ntime_sum"]))
+    assert out.shape == g["out"].shape
+    assert np.allclose(out, g["out"], rtol=1e-5, atol=1e-4)
+    one = orc.beam_power_sum_single(g["x"], int(g["ntime_sum"]), 1)
+    assert np.allclose(one, g["out"][1], rtol=1e-5, atol=1e-4)
