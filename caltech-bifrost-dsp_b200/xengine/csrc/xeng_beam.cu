@@ -1,0 +1,234 @@
+// Beamform + beam-power integration for sm_100a.
+//
+// bfBeamformRun  (call site /root/reference/pipeline/lwa352_pipeline/blocks/beamform_block.py:449):
+//     out[c][b][t] = sum_i w[c][b][i] * v[t][c][i]         complex fp32, no conjugation
+//     (pinned by pipeline/verification/tests/beamformer/beamformer_test.py:76-84)
+// bfBeamformIntegrate / ...SingleBeam (beamform_sum_beams_block.py:245, beamform_sum_single_beam_block.py:114):
+//     out[p][T][c][0..3] = sum_{t in T} [ |X|^2, |Y|^2, Re X Y*, Im X Y* ],  X = beam 2p, Y = beam 2p+1
+//     (pinned by pipeline/verification/tests/beamformer/beamformer_sum_test.py:64-77)
+//
+// The contraction is done in fp32 on the FMA pipe (bit-for-bit fp32 weights, exact integer voltages):
+// a CTA owns (channel, 128 time samples, 32 beams); 4+4-bit voltages are unpacked once per 64-input
+// chunk into shared memory as complex fp32 and reused by all 32 beams; each thread keeps a
+// 4-beam x 4-time complex register tile (64 FFMA per 4 LDS.128).
+#include "xeng_internal.h"
+
+namespace xeng {
+namespace {
+
+constexpr int BB = 32;    // beams per CTA
+constexpr int TT = 128;   // time samples per CTA
+constexpr int IK = 64;    // inputs per shared-memory chunk
+constexpr int BF_THREADS = 256;
+
+struct BeamSmem {
+  float2 v[IK][TT];   // 64 KB
+  float2 w[BB][IK];   // 16 KB
+};
+
+__device__ __forceinline__ void load_v32(const BeamArgs& a, int c, int t, int i0, bool vec_ok, uint4 (&raw)[2]) {
+  raw[0] = raw[1] = make_uint4(0, 0, 0, 0);
+  if (t >= a.ntime) return;
+  const uint8_t* p = a.in + (static_cast<long>(t) * a.nchan + c) * a.ninput;
+  if (vec_ok && i0 + 32 <= a.ninput) {
+    raw[0] = __ldg(reinterpret_cast<const uint4*>(p + i0));
+    raw[1] = __ldg(reinterpret_cast<const uint4*>(p + i0 + 16));
+  } else {
+    uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int k = 0; k < 32; ++k)
+      if (i0 + k < a.ninput) w[k >> 2] |= static_cast<uint32_t>(p[i0 + k]) << (8 * (k & 3));
+    raw[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    raw[1] = make_uint4(w[4], w[5], w[6], w[7]);
+  }
+}
+
+__device__ __forceinline__ float2 decode44(uint32_t byte) {
+  const int b = static_cast<int>(byte);
+  const int re = (b << 24) >> 28;   // high nibble, sign-extended
+  const int im = (b << 28) >> 28;   // low nibble, sign-extended
+  return make_float2(static_cast<float>(re), static_cast<float>(im));
+}
+
+__global__ void __launch_bounds__(BF_THREADS, 2) beamform_kernel(BeamArgs a) {
+  extern __shared__ __align__(16) uint8_t bf_smem[];
+  BeamSmem& S = *reinterpret_cast<BeamSmem*>(bf_smem);
+  const int tid = threadIdx.x;
+  const int t0 = blockIdx.x * TT, c = blockIdx.y, b0 = blockIdx.z * BB;
+  const int tb = tid >> 5, tt = tid & 31;
+
+  // staging roles
+  const int vt = tid & (TT - 1), vhalf = tid >> 7;     // v: time sample, which 32-input half of the chunk
+  const bool vec_ok = (a.ninput % 16 == 0) && ((reinterpret_cast<uintptr_t>(a.in) & 15) == 0);
+  const bool wvec_ok = (a.ninput % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.w) & 15) == 0);
+
+  float2 acc[4][4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) acc[j][k] = make_float2(0.f, 0.f);
+
+  const int nchunk = (a.ninput + IK - 1) / IK;
+  uint4 vraw[2];
+  float4 wraw[4];
+  auto load_w = [&](int i0) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int idx = j * BF_THREADS + tid;
+      const int b = idx >> 5, i2 = idx & 31;       // 32 float4 (= 64 inputs) per beam row
+      const int i = i0 + 2 * i2;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (b0 + b < a.nbeam && i < a.ninput) {
+        const float2* wp = a.w + (static_cast<long>(c) * a.nbeam + (b0 + b)) * a.ninput + i;
+        if (wvec_ok && i + 1 < a.ninput) {
+          v = __ldg(reinterpret_cast<const float4*>(wp));
+        } else {
+          const float2 x = wp[0];
+          v.x = x.x; v.y = x.y;
+          if (i + 1 < a.ninput) { const float2 y = wp[1]; v.z = y.x; v.w = y.y; }
+        }
+      }
+      wraw[j] = v;
+    }
+  };
+  load_v32(a, c, t0 + vt, vhalf * 32, vec_ok, vraw);
+  load_w(0);
+
+  for (int ch = 0; ch < nchunk; ++ch) {
+    __syncthreads();  // previous chunk fully consumed
+    {
+      const uint32_t words[8] = {vraw[0].x, vraw[0].y, vraw[0].z, vraw[0].w, vraw[1].x, vraw[1].y, vraw[1].z, vraw[1].w};
+#pragma unroll
+      for (int k = 0; k < 32; ++k) S.v[vhalf * 32 + k][vt] = decode44((words[k >> 2] >> (8 * (k & 3))) & 0xFF);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int idx = j * BF_THREADS + tid;
+        *reinterpret_cast<float4*>(&S.w[idx >> 5][2 * (idx & 31)]) = wraw[j];
+      }
+    }
+    __syncthreads();
+    if (ch + 1 < nchunk) {  // prefetch next chunk into registers while computing this one
+      load_v32(a, c, t0 + vt, (ch + 1) * IK + vhalf * 32, vec_ok, vraw);
+      load_w((ch + 1) * IK);
+    }
+#pragma unroll 4
+    for (int i = 0; i < IK; i += 2) {
+      float4 wv[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) wv[j] = *reinterpret_cast<const float4*>(&S.w[4 * tb + j][i]);
+      const float4 va0 = *reinterpret_cast<const float4*>(&S.v[i][4 * tt]);
+      const float4 va1 = *reinterpret_cast<const float4*>(&S.v[i][4 * tt + 2]);
+      const float4 vb0 = *reinterpret_cast<const float4*>(&S.v[i + 1][4 * tt]);
+      const float4 vb1 = *reinterpret_cast<const float4*>(&S.v[i + 1][4 * tt + 2]);
+      const float2 va[4] = {make_float2(va0.x, va0.y), make_float2(va0.z, va0.w), make_float2(va1.x, va1.y),
+                            make_float2(va1.z, va1.w)};
+      const float2 vb[4] = {make_float2(vb0.x, vb0.y), make_float2(vb0.z, vb0.w), make_float2(vb1.x, vb1.y),
+                            make_float2(vb1.z, vb1.w)};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          float re = acc[j][k].x, im = acc[j][k].y;
+          re = fmaf(wv[j].x, va[k].x, re);
+          re = fmaf(-wv[j].y, va[k].y, re);
+          im = fmaf(wv[j].x, va[k].y, im);
+          im = fmaf(wv[j].y, va[k].x, im);
+          re = fmaf(wv[j].z, vb[k].x, re);
+          re = fmaf(-wv[j].w, vb[k].y, re);
+          im = fmaf(wv[j].z, vb[k].y, im);
+          im = fmaf(wv[j].w, vb[k].x, im);
+          acc[j][k] = make_float2(re, im);
+        }
+      }
+    }
+  }
+
+  const int t = t0 + 4 * tt;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int b = b0 + 4 * tb + j;
+    if (b >= a.nbeam) continue;
+    float2* o = a.out + (static_cast<long>(c) * a.nbeam + b) * a.ntime + t;
+    if (t + 3 < a.ntime && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+      reinterpret_cast<float4*>(o)[0] = make_float4(acc[j][0].x, acc[j][0].y, acc[j][1].x, acc[j][1].y);
+      reinterpret_cast<float4*>(o)[1] = make_float4(acc[j][2].x, acc[j][2].y, acc[j][3].x, acc[j][3].y);
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (t + k < a.ntime) o[k] = acc[j][k];
+    }
+  }
+}
+
+// One block per (channel, dual-pol beam): per-sample products go to shared memory with coalesced
+// loads, then one thread per output time block sums ntime_sum of them in time order.
+constexpr int PW_T = 1024;
+__global__ void __launch_bounds__(256) beam_integrate_kernel(const float2* __restrict__ in, float4* __restrict__ out,
+                                                             int nchan, int nbeam, int ntime, int ntime_sum,
+                                                             int beam0, int nbeam_out) {
+  __shared__ float4 prod[PW_T];
+  const int c = blockIdx.x, p = blockIdx.y;
+  const float2* X = in + (static_cast<long>(c) * nbeam + 2 * (beam0 + p)) * ntime;
+  const float2* Y = X + ntime;
+  const int nblk = ntime / ntime_sum;
+  const int span = (PW_T / ntime_sum) * ntime_sum;   // whole output blocks per pass
+  if (span == 0) {
+    // ntime_sum > PW_T: one thread per output block walks global memory directly
+    for (int T = threadIdx.x; T < nblk; T += blockDim.x) {
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int k = 0; k < ntime_sum; ++k) {
+        const float2 x = X[T * ntime_sum + k], y = Y[T * ntime_sum + k];
+        s.x += x.x * x.x + x.y * x.y;
+        s.y += y.x * y.x + y.y * y.y;
+        s.z += x.x * y.x + x.y * y.y;
+        s.w += x.y * y.x - x.x * y.y;
+      }
+      out[(static_cast<long>(p) * nblk + T) * nchan + c] = s;
+    }
+    return;
+  }
+  for (int tbase = 0; tbase < nblk * ntime_sum; tbase += span) {
+    const int n = min(span, nblk * ntime_sum - tbase);
+    for (int k = threadIdx.x; k < n; k += blockDim.x) {
+      const float2 x = X[tbase + k], y = Y[tbase + k];
+      prod[k] = make_float4(x.x * x.x + x.y * x.y, y.x * y.x + y.y * y.y, x.x * y.x + x.y * y.y,
+                            x.y * y.x - x.x * y.y);
+    }
+    __syncthreads();
+    for (int T = threadIdx.x; T < n / ntime_sum; T += blockDim.x) {
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int k = 0; k < ntime_sum; ++k) {
+        const float4 q = prod[T * ntime_sum + k];
+        s.x += q.x; s.y += q.y; s.z += q.z; s.w += q.w;
+      }
+      out[(static_cast<long>(p) * nblk + tbase / ntime_sum + T) * nchan + c] = s;
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace
+
+cudaError_t launch_beamform(const BeamArgs& a, cudaStream_t stream) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(beamform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(sizeof(BeamSmem)));
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  if (a.ntime <= 0 || a.nchan <= 0 || a.nbeam <= 0) return cudaSuccess;
+  dim3 grid((a.ntime + TT - 1) / TT, a.nchan, (a.nbeam + BB - 1) / BB);
+  beamform_kernel<<<grid, BF_THREADS, sizeof(BeamSmem), stream>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_beam_integrate(const float2* in, float* out, int nchan, int nbeam, int ntime, int ntime_sum,
+                                  int beam0, int nbeam_out, cudaStream_t stream) {
+  if (nchan <= 0 || nbeam_out <= 0 || ntime / ntime_sum <= 0) return cudaSuccess;
+  dim3 grid(nchan, nbeam_out);
+  beam_integrate_kernel<<<grid, 256, 0, stream>>>(in, reinterpret_cast<float4*>(out), nchan, nbeam, ntime, ntime_sum,
+                                                  beam0, nbeam_out);
+  return cudaGetLastError();
+}
+
+}  // namespace xeng

@@ -1,0 +1,106 @@
+/*
+ * libxeng -- C ABI of the B200-native LWA-352 X-engine hot path.
+ *
+ * This is the drop-in boundary: every entry point replaces one of the ctypes `_bf.*` calls the
+ * reference blocks make (paths below are relative to /root/reference/pipeline/lwa352_pipeline/blocks).
+ * Plain pointers and sizes only; the caller owns every buffer, the library owns opaque handles.
+ * All functions return 0 (XENG_OK) on success and a negative code on failure; the message of the most
+ * recent failure on the calling thread is returned by xeng_last_error().  No exceptions cross this
+ * boundary.  Work is enqueued on the handle's CUDA stream (default: the legacy default stream, which
+ * is also torch's default stream); call the *_sync function before committing an output span, as the
+ * reference does with stream_synchronize()/BFSync().  There is no CPU fallback anywhere in this library.
+ */
+#ifndef XENG_H_
+#define XENG_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define XENG_OK 0
+#define XENG_ERR_ARG (-1)     /* invalid argument / unsupported shape */
+#define XENG_ERR_CUDA (-2)    /* a CUDA runtime call or kernel failed */
+#define XENG_ERR_NOMEM (-3)   /* device allocation failed */
+#define XENG_ERR_WATCHDOG (-4)/* in-kernel pipeline watchdog fired */
+
+const char* xeng_last_error(void);
+int xeng_version(void);
+/* Number of CUDA devices visible; <0 on error.  The library fails loudly when there is none. */
+int xeng_device_count(void);
+
+/* ------------------------------------------------------------------ Corr (xGPU replacement) */
+typedef struct xeng_corr_s* xeng_corr_t;
+
+/* Replaces bfXgpuInitialize(in, out, gpu) -- corr_block.py:253.  gpu = -1 keeps the current device.
+ * npol must be 2 and nstand even (xGPU register-tile order, corr_block.py:37-58). */
+int xeng_corr_create(xeng_corr_t* h, int nstand, int npol, int nchan, int ntime_gulp, int gpu);
+int xeng_corr_destroy(xeng_corr_t h);
+int xeng_corr_set_stream(xeng_corr_t h, void* cuda_stream);
+/* 0 = tcgen05 tensor-core kernel (default), 1 = CUDA-core cross-check kernel (tests only). */
+int xeng_corr_set_impl(xeng_corr_t h, int impl);
+/* int32 words per plane: nchan*(nstand/2+1)*(nstand/4)*npol*npol*4 -- corr_block.py:231.
+ * The output buffer holds 2*matlen int32: real plane, then imaginary plane. */
+int64_t xeng_corr_matlen(xeng_corr_t h);
+
+/* Replaces bfXgpuKernel(in, out, doDump) -- corr_block.py:445.
+ * d_in : device u8 [ntime_gulp][nchan][nstand][npol], byte = (re<<4)|(im&0xF)  (corr_block.py:270-275)
+ * d_out: device int32 [2][nchan][matlen/nchan] in xGPU register-tile order; written only when do_dump != 0.
+ * Integrates internally across calls; on do_dump the integration is written to d_out and cleared.
+ * Word regtile_index(in0,in1) holds sum_t conj(v[in0]) v[in1] (pipeline/verification/xgpu_test.py:102-136). */
+int xeng_corr_run(xeng_corr_t h, const void* d_in, void* d_out, int do_dump);
+
+/* Replaces bfXgpuCorrelate(in, out, doDump) (host-memory variant, pipeline/verification/xgpu_test.py:86-89):
+ * same as xeng_corr_run but h_in / h_out are HOST buffers; copies are done inside, and the call
+ * returns after the result (if do_dump) is in h_out. */
+int xeng_corr_run_host(xeng_corr_t h, const void* h_in, void* h_out, int do_dump);
+
+/* Fused Corr + CorrAcc step (corr_block.py:445 followed by corr_acc_block.py:299-306):
+ * d_acc = X(d_in) when first != 0, else d_acc += X(d_in); the read-modify-write is done by the
+ * bulk-reduce engine in L2, no intermediate visibility buffer is written. */
+int xeng_corr_accumulate(xeng_corr_t h, const void* d_in, void* d_acc, int first);
+int xeng_corr_sync(xeng_corr_t h);
+
+/* Replaces bfXgpuGetOrder(antpol_to_input, antpol_to_bl, bl_is_conj) -- corr_block.py:331-333.  HOST arrays.
+ * a2i [nstand][npol]; a2bl, conj [nstand][nstand][npol][npol].  a2bl = word index inside one channel of the
+ * xGPU buffer, conj = 1 if that word must be conjugated to read as v(s0,p0) conj(v(s1,p1)). */
+int xeng_get_order(const int32_t* a2i, int32_t* a2bl, int32_t* conj, int nstand, int npol);
+
+/* ------------------------------------------------------------------ CorrAcc / CorrSubsel / reorder */
+/* Replaces BFMap("a = b") / BFMap("a += b") -- corr_acc_block.py:299-306.  Device pointers, n int32 words. */
+int xeng_acc(void* d_acc, const void* d_in, size_t n, int first, void* cuda_stream);
+
+/* Replaces bfXgpuSubSelect(in, out, vismap, conj, nchan_sum, 0) -- corr_subsel_block.py:298.
+ * d_in int32 [2][nchan][words_per_chan]; d_out int32 [nchan/nchan_sum][nvis][2] (re,im interleaved);
+ * d_vismap, d_conj device int32 [nvis]. */
+int xeng_subsel(const void* d_in, void* d_out, const void* d_vismap, const void* d_conj, int nvis, int nchan,
+                int nchan_sum, int64_t words_per_chan, void* cuda_stream);
+
+/* Replaces bfXgpuReorder(in, out, a2bl, conj) -- corr_output_full_block.py:669 (a CPU loop in the reference;
+ * a device kernel here).  d_out int32 [nstand][nstand][npol][npol][nchan][2] = v(s0,p0) conj(v(s1,p1)). */
+int xeng_reorder(const void* d_in, void* d_out, const void* d_a2bl, const void* d_conj, int nstand, int npol,
+                 int nchan, int64_t words_per_chan, void* cuda_stream);
+
+/* ------------------------------------------------------------------ Beamform / BeamformSum */
+typedef struct xeng_bf_s* xeng_bf_t;
+
+/* Replaces bfBeamformInitialize(gpu, ninput, nchan, ntime, nbeam, ntime_blocks) -- beamform_block.py:251-253. */
+int xeng_bf_create(xeng_bf_t* h, int gpu, int ninput, int nchan, int ntime, int nbeam, int ntime_blocks);
+int xeng_bf_destroy(xeng_bf_t h);
+int xeng_bf_set_stream(xeng_bf_t h, void* cuda_stream);
+/* Replaces bfBeamformRun(in, out, weights) -- beamform_block.py:449.
+ * d_in u8 [ntime][nchan][ninput]; d_weights cf32 [nchan][nbeam][ninput]; d_out cf32 [nchan][nbeam][ntime]. */
+int xeng_bf_run(xeng_bf_t h, const void* d_in, void* d_out, const void* d_weights);
+/* Replaces bfBeamformIntegrate(in, out, ntime_sum) -- beamform_sum_beams_block.py:245, beamform_sum_block.py:116.
+ * d_in cf32 [nchan][nbeam][ntime]; d_out f32 [nbeam/2][ntime/ntime_sum][nchan][4]. */
+int xeng_bf_integrate(xeng_bf_t h, const void* d_in, void* d_out, int ntime_sum);
+/* Replaces bfBeamformIntegrateSingleBeam(in, out, ntime_sum, beam_id) -- beamform_sum_single_beam_block.py:114.
+ * d_out f32 [ntime/ntime_sum][nchan][4] for dual-pol beam beam_id. */
+int xeng_bf_integrate_single(xeng_bf_t h, const void* d_in, void* d_out, int ntime_sum, int beam_id);
+int xeng_bf_sync(xeng_bf_t h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* XENG_H_ */
