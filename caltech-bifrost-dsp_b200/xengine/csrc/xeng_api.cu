@@ -1,0 +1,321 @@
+// libxeng C ABI (see include/xeng.h).  Host-side glue only: argument checks, handle state, launches.
+// No CPU arithmetic path exists here: every entry point either launches a CUDA kernel or fails.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "../../../include/xeng.h"
+#include "xeng_internal.h"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define XENG_CUDA(expr)                                                                       \
+  do {                                                                                        \
+    cudaError_t e__ = (expr);                                                                 \
+    if (e__ != cudaSuccess)                                                                   \
+      return fail(e__ == cudaErrorMemoryAllocation ? XENG_ERR_NOMEM : XENG_ERR_CUDA, "%s: %s", \
+                  #expr, cudaGetErrorString(e__));                                            \
+  } while (0)
+
+int select_device(int gpu) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n <= 0)
+    return fail(XENG_ERR_CUDA, "no CUDA device available (%s); libxeng has no CPU path",
+                e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+  if (gpu >= n) return fail(XENG_ERR_ARG, "gpu %d out of range (%d devices)", gpu, n);
+  if (gpu >= 0) XENG_CUDA(cudaSetDevice(gpu));
+  return XENG_OK;
+}
+
+}  // namespace
+
+struct xeng_corr_s {
+  int nstand, npol, nchan, ntime, ninput, device, nsm, impl;
+  long words_per_chan, quad_cells;
+  int64_t matlen;
+  cudaStream_t stream;
+  int32_t* d_acc;      // internal integration (2*matlen words), allocated on first multi-call integration
+  bool acc_live;       // d_acc holds a partial integration
+  int* h_err;          // mapped pinned watchdog word
+  int* d_err;
+  uint8_t* d_stage_in; // staging for the host-memory variant
+  int32_t* d_stage_out;
+};
+
+struct xeng_bf_s {
+  int device, ninput, nchan, ntime, nbeam, ntime_blocks;
+  cudaStream_t stream;
+};
+
+extern "C" {
+
+const char* xeng_last_error(void) { return g_err; }
+int xeng_version(void) { return 100; }
+int xeng_device_count(void) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) return fail(XENG_ERR_CUDA, "cudaGetDeviceCount: %s", cudaGetErrorString(e));
+  return n;
+}
+
+// ------------------------------------------------------------------------------------------ Corr
+int xeng_corr_create(xeng_corr_t* out, int nstand, int npol, int nchan, int ntime_gulp, int gpu) {
+  if (!out) return fail(XENG_ERR_ARG, "null handle pointer");
+  *out = nullptr;
+  if (npol != 2) return fail(XENG_ERR_ARG, "npol must be 2 (xGPU register-tile order), got %d", npol);
+  if (nstand <= 0 || (nstand & 3))   // corr_block.py:231 and :50 agree on the buffer size only when 4 | nstand
+    return fail(XENG_ERR_ARG, "nstand must be a positive multiple of 4, got %d", nstand);
+  if (nchan <= 0 || ntime_gulp <= 0) return fail(XENG_ERR_ARG, "nchan and ntime_gulp must be positive");
+  int rc = select_device(gpu);
+  if (rc) return rc;
+  xeng_corr_s* h = new (std::nothrow) xeng_corr_s();
+  if (!h) return fail(XENG_ERR_NOMEM, "host allocation failed");
+  memset(h, 0, sizeof(*h));
+  h->nstand = nstand; h->npol = npol; h->nchan = nchan; h->ntime = ntime_gulp;
+  h->ninput = nstand * npol;
+  h->quad_cells = static_cast<long>(nstand / 2 + 1) * nstand / 4;
+  h->words_per_chan = h->quad_cells * 16;
+  h->matlen = static_cast<int64_t>(nchan) * h->words_per_chan;
+  cudaError_t e = cudaGetDevice(&h->device);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->nsm, cudaDevAttrMultiProcessorCount, h->device);
+  if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void**>(&h->h_err), sizeof(int), cudaHostAllocMapped);
+  if (e == cudaSuccess) {
+    *h->h_err = 0;
+    e = cudaHostGetDevicePointer(reinterpret_cast<void**>(&h->d_err), h->h_err, 0);
+  }
+  if (e != cudaSuccess) {
+    if (h->h_err) cudaFreeHost(h->h_err);
+    delete h;
+    return fail(XENG_ERR_CUDA, "xeng_corr_create: %s", cudaGetErrorString(e));
+  }
+  *out = h;
+  return XENG_OK;
+}
+
+int xeng_corr_destroy(xeng_corr_t h) {
+  if (!h) return XENG_OK;
+  cudaSetDevice(h->device);
+  if (h->d_acc) cudaFree(h->d_acc);
+  if (h->d_stage_in) cudaFree(h->d_stage_in);
+  if (h->d_stage_out) cudaFree(h->d_stage_out);
+  if (h->h_err) cudaFreeHost(h->h_err);
+  delete h;
+  return XENG_OK;
+}
+
+int xeng_corr_set_stream(xeng_corr_t h, void* s) {
+  if (!h) return fail(XENG_ERR_ARG, "null handle");
+  h->stream = static_cast<cudaStream_t>(s);
+  return XENG_OK;
+}
+int xeng_corr_set_impl(xeng_corr_t h, int impl) {
+  if (!h) return fail(XENG_ERR_ARG, "null handle");
+  if (impl != 0 && impl != 1) return fail(XENG_ERR_ARG, "impl must be 0 (tcgen05) or 1 (CUDA-core cross-check)");
+  h->impl = impl;
+  return XENG_OK;
+}
+int64_t xeng_corr_matlen(xeng_corr_t h) { return h ? h->matlen : 0; }
+
+static int corr_launch(xeng_corr_t h, const void* d_in, int32_t* d_out, int accumulate) {
+  xeng::CorrArgs a;
+  a.in = static_cast<const uint8_t*>(d_in);
+  a.out = d_out;
+  a.err = h->d_err;
+  a.ntime = h->ntime; a.nchan = h->nchan; a.ninput = h->ninput;
+  a.npairs = h->nstand / 2;
+  const int T = (h->ninput + 127) / 128;
+  a.tiles_per_chan = T * (T + 1) / 2;
+  a.ntiles = a.tiles_per_chan * h->nchan;
+  a.accumulate = accumulate;
+  a.words_per_chan = h->words_per_chan;
+  a.quad_cells = h->quad_cells;
+  XENG_CUDA(h->impl == 0 ? xeng::launch_corr_tc(a, h->nsm, h->stream) : xeng::launch_corr_simt(a, h->stream));
+  return XENG_OK;
+}
+
+static int corr_check(xeng_corr_t h, const void* in, const void* out, bool need_out) {
+  if (!h) return fail(XENG_ERR_ARG, "null handle");
+  if (!in) return fail(XENG_ERR_ARG, "null input pointer");
+  if (need_out && !out) return fail(XENG_ERR_ARG, "null output pointer");
+  XENG_CUDA(cudaSetDevice(h->device));
+  return XENG_OK;
+}
+
+int xeng_corr_run(xeng_corr_t h, const void* d_in, void* d_out, int do_dump) {
+  int rc = corr_check(h, d_in, d_out, do_dump != 0);
+  if (rc) return rc;
+  const size_t bytes = static_cast<size_t>(2 * h->matlen) * sizeof(int32_t);
+  if (do_dump && !h->acc_live)  // single-gulp integration: straight into the caller's buffer
+    return corr_launch(h, d_in, static_cast<int32_t*>(d_out), 0);
+  if (!h->d_acc) XENG_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->d_acc), bytes));
+  rc = corr_launch(h, d_in, h->d_acc, h->acc_live ? 1 : 0);
+  if (rc) return rc;
+  h->acc_live = true;
+  if (do_dump) {
+    XENG_CUDA(cudaMemcpyAsync(d_out, h->d_acc, bytes, cudaMemcpyDeviceToDevice, h->stream));
+    h->acc_live = false;  // next call overwrites: this is xGPU's "clear on dump"
+  }
+  return XENG_OK;
+}
+
+int xeng_corr_accumulate(xeng_corr_t h, const void* d_in, void* d_acc, int first) {
+  int rc = corr_check(h, d_in, d_acc, true);
+  if (rc) return rc;
+  return corr_launch(h, d_in, static_cast<int32_t*>(d_acc), first ? 0 : 1);
+}
+
+int xeng_corr_sync(xeng_corr_t h) {
+  if (!h) return fail(XENG_ERR_ARG, "null handle");
+  cudaError_t e = cudaStreamSynchronize(h->stream);
+  if (h->h_err && *h->h_err != 0)
+    return fail(XENG_ERR_WATCHDOG, "corr kernel watchdog fired at barrier tag %d (%s)", *h->h_err,
+                cudaGetErrorString(e));
+  if (e != cudaSuccess) return fail(XENG_ERR_CUDA, "cudaStreamSynchronize: %s", cudaGetErrorString(e));
+  return XENG_OK;
+}
+
+int xeng_corr_run_host(xeng_corr_t h, const void* h_in, void* h_out, int do_dump) {
+  int rc = corr_check(h, h_in, h_out, do_dump != 0);
+  if (rc) return rc;
+  const size_t in_bytes = static_cast<size_t>(h->ntime) * h->nchan * h->ninput;
+  const size_t out_bytes = static_cast<size_t>(2 * h->matlen) * sizeof(int32_t);
+  if (!h->d_stage_in) XENG_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->d_stage_in), in_bytes));
+  if (do_dump && !h->d_stage_out) XENG_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->d_stage_out), out_bytes));
+  XENG_CUDA(cudaMemcpyAsync(h->d_stage_in, h_in, in_bytes, cudaMemcpyHostToDevice, h->stream));
+  rc = xeng_corr_run(h, h->d_stage_in, h->d_stage_out, do_dump);
+  if (rc) return rc;
+  if (do_dump) XENG_CUDA(cudaMemcpyAsync(h_out, h->d_stage_out, out_bytes, cudaMemcpyDeviceToHost, h->stream));
+  return xeng_corr_sync(h);
+}
+
+// bfXgpuGetOrder: host-only index bookkeeping (the reference computes it on the CPU as well).
+int xeng_get_order(const int32_t* a2i, int32_t* a2bl, int32_t* conj, int nstand, int npol) {
+  if (!a2i || !a2bl || !conj) return fail(XENG_ERR_ARG, "null pointer");
+  if (npol != 2 || nstand <= 0 || (nstand & 3)) return fail(XENG_ERR_ARG, "need npol == 2 and 4 | nstand");
+  const long Q = static_cast<long>(nstand / 2 + 1) * nstand / 4;
+  for (int i = 0; i < nstand * npol; ++i)
+    if (a2i[i] < 0 || a2i[i] >= nstand * npol) return fail(XENG_ERR_ARG, "ant_to_input[%d] = %d out of range", i, a2i[i]);
+  for (int s0 = 0; s0 < nstand; ++s0)
+    for (int s1 = 0; s1 < nstand; ++s1)
+      for (int p0 = 0; p0 < npol; ++p0)
+        for (int p1 = 0; p1 < npol; ++p1) {
+          const int i0 = a2i[s0 * npol + p0], i1 = a2i[s1 * npol + p1];
+          const bool stored = (i1 >> 1) >= (i0 >> 1);   // word (i0,i1) exists and holds conj(v_i0) v_i1
+          const int lo = stored ? i0 : i1, hi = stored ? i1 : i0;
+          const int a0 = lo >> 1, a1 = hi >> 1;
+          const long tri = static_cast<long>(a1 / 2) * (a1 / 2 + 1) / 2 + a0 / 2;
+          const long cell = (2 * (a0 & 1) + (a1 & 1)) * Q + tri;
+          const long o = ((static_cast<long>(s0) * nstand + s1) * npol + p0) * npol + p1;
+          a2bl[o] = static_cast<int32_t>(cell * 4 + 2 * (hi & 1) + (lo & 1));
+          conj[o] = stored ? 1 : 0;
+        }
+  return XENG_OK;
+}
+
+// ------------------------------------------------------------------ CorrAcc / CorrSubsel / reorder
+int xeng_acc(void* d_acc, const void* d_in, size_t n, int first, void* stream) {
+  if (!d_acc || !d_in) return fail(XENG_ERR_ARG, "null pointer");
+  XENG_CUDA(xeng::launch_acc(static_cast<int32_t*>(d_acc), static_cast<const int32_t*>(d_in), n, first,
+                             static_cast<cudaStream_t>(stream)));
+  return XENG_OK;
+}
+
+int xeng_subsel(const void* d_in, void* d_out, const void* d_vismap, const void* d_conj, int nvis, int nchan,
+                int nchan_sum, int64_t words_per_chan, void* stream) {
+  if (!d_in || !d_out || !d_vismap || !d_conj) return fail(XENG_ERR_ARG, "null pointer");
+  if (nvis < 0 || nchan <= 0 || nchan_sum <= 0 || words_per_chan <= 0) return fail(XENG_ERR_ARG, "bad sizes");
+  XENG_CUDA(xeng::launch_subsel(static_cast<const int32_t*>(d_in), static_cast<int32_t*>(d_out),
+                                static_cast<const int32_t*>(d_vismap), static_cast<const int32_t*>(d_conj), nvis,
+                                nchan, nchan_sum, words_per_chan, static_cast<cudaStream_t>(stream)));
+  return XENG_OK;
+}
+
+int xeng_reorder(const void* d_in, void* d_out, const void* d_a2bl, const void* d_conj, int nstand, int npol,
+                 int nchan, int64_t words_per_chan, void* stream) {
+  if (!d_in || !d_out || !d_a2bl || !d_conj) return fail(XENG_ERR_ARG, "null pointer");
+  if (nstand <= 0 || npol <= 0 || nchan <= 0) return fail(XENG_ERR_ARG, "bad sizes");
+  XENG_CUDA(xeng::launch_reorder(static_cast<const int32_t*>(d_in), static_cast<int32_t*>(d_out),
+                                 static_cast<const int32_t*>(d_a2bl), static_cast<const int32_t*>(d_conj), nstand,
+                                 npol, nchan, words_per_chan, static_cast<cudaStream_t>(stream)));
+  return XENG_OK;
+}
+
+// ------------------------------------------------------------------------------------ Beamform
+int xeng_bf_create(xeng_bf_t* out, int gpu, int ninput, int nchan, int ntime, int nbeam, int ntime_blocks) {
+  if (!out) return fail(XENG_ERR_ARG, "null handle pointer");
+  *out = nullptr;
+  if (ninput <= 0 || nchan <= 0 || ntime <= 0 || nbeam <= 0) return fail(XENG_ERR_ARG, "sizes must be positive");
+  int rc = select_device(gpu);
+  if (rc) return rc;
+  xeng_bf_s* h = new (std::nothrow) xeng_bf_s();
+  if (!h) return fail(XENG_ERR_NOMEM, "host allocation failed");
+  h->ninput = ninput; h->nchan = nchan; h->ntime = ntime; h->nbeam = nbeam; h->ntime_blocks = ntime_blocks;
+  h->stream = nullptr;
+  cudaError_t e = cudaGetDevice(&h->device);
+  if (e != cudaSuccess) {
+    delete h;
+    return fail(XENG_ERR_CUDA, "cudaGetDevice: %s", cudaGetErrorString(e));
+  }
+  *out = h;
+  return XENG_OK;
+}
+int xeng_bf_destroy(xeng_bf_t h) {
+  delete h;
+  return XENG_OK;
+}
+int xeng_bf_set_stream(xeng_bf_t h, void* s) {
+  if (!h) return fail(XENG_ERR_ARG, "null handle");
+  h->stream = static_cast<cudaStream_t>(s);
+  return XENG_OK;
+}
+
+int xeng_bf_run(xeng_bf_t h, const void* d_in, void* d_out, const void* d_w) {
+  if (!h || !d_in || !d_out || !d_w) return fail(XENG_ERR_ARG, "null pointer");
+  XENG_CUDA(cudaSetDevice(h->device));
+  xeng::BeamArgs a;
+  a.in = static_cast<const uint8_t*>(d_in);
+  a.w = static_cast<const float2*>(d_w);
+  a.out = static_cast<float2*>(d_out);
+  a.ntime = h->ntime; a.nchan = h->nchan; a.ninput = h->ninput; a.nbeam = h->nbeam;
+  XENG_CUDA(xeng::launch_beamform(a, h->stream));
+  return XENG_OK;
+}
+
+int xeng_bf_integrate(xeng_bf_t h, const void* d_in, void* d_out, int ntime_sum) {
+  if (!h || !d_in || !d_out) return fail(XENG_ERR_ARG, "null pointer");
+  if (ntime_sum <= 0 || (h->nbeam & 1)) return fail(XENG_ERR_ARG, "need ntime_sum > 0 and an even number of beams");
+  XENG_CUDA(cudaSetDevice(h->device));
+  XENG_CUDA(xeng::launch_beam_integrate(static_cast<const float2*>(d_in), static_cast<float*>(d_out), h->nchan,
+                                        h->nbeam, h->ntime, ntime_sum, 0, h->nbeam / 2, h->stream));
+  return XENG_OK;
+}
+
+int xeng_bf_integrate_single(xeng_bf_t h, const void* d_in, void* d_out, int ntime_sum, int beam_id) {
+  if (!h || !d_in || !d_out) return fail(XENG_ERR_ARG, "null pointer");
+  if (ntime_sum <= 0 || beam_id < 0 || 2 * beam_id + 1 >= h->nbeam) return fail(XENG_ERR_ARG, "bad ntime_sum / beam_id");
+  XENG_CUDA(cudaSetDevice(h->device));
+  XENG_CUDA(xeng::launch_beam_integrate(static_cast<const float2*>(d_in), static_cast<float*>(d_out), h->nchan,
+                                        h->nbeam, h->ntime, ntime_sum, beam_id, 1, h->stream));
+  return XENG_OK;
+}
+
+int xeng_bf_sync(xeng_bf_t h) {
+  if (!h) return fail(XENG_ERR_ARG, "null handle");
+  cudaError_t e = cudaStreamSynchronize(h->stream);
+  if (e != cudaSuccess) return fail(XENG_ERR_CUDA, "cudaStreamSynchronize: %s", cudaGetErrorString(e));
+  return XENG_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,128 @@
+"""Python faces of the libxeng entry points, one per `_bf.*` call the reference blocks make.
+
+Buffers are anything `_lib.ptr` understands (torch CUDA tensors in this repo's tests and bench, bifrost
+ndarrays in a bifrost pipeline).  Nothing here computes on the CPU.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import check, ptr
+
+
+def words_per_chan(nstand, npol=2):
+    """corr_block.py:231 with nchan = 1."""
+    return (nstand // 2 + 1) * (nstand // 4) * npol * npol * 4
+
+
+class XCorr(object):
+    """xGPU stand-in: bfXgpuInitialize (corr_block.py:253) + bfXgpuKernel (corr_block.py:445)."""
+
+    def __init__(self, nstand=352, npol=2, nchan=192, ntime_gulp=480, gpu=-1, stream=None):
+        self._lib = _lib.load()
+        self._h = C.c_void_p()
+        check(self._lib.xeng_corr_create(C.byref(self._h), nstand, npol, nchan, ntime_gulp, gpu), "xeng_corr_create")
+        self.nstand, self.npol, self.nchan, self.ntime_gulp = nstand, npol, nchan, ntime_gulp
+        self.matlen = int(self._lib.xeng_corr_matlen(self._h))
+        if stream is not None:
+            self.set_stream(stream)
+
+    def set_stream(self, stream):
+        check(self._lib.xeng_corr_set_stream(self._h, ptr(stream)), "xeng_corr_set_stream")
+
+    def set_impl(self, impl):
+        check(self._lib.xeng_corr_set_impl(self._h, int(impl)), "xeng_corr_set_impl")
+
+    def run(self, d_in, d_out, do_dump):
+        """bfXgpuKernel(in, out, doDump)."""
+        check(self._lib.xeng_corr_run(self._h, ptr(d_in), ptr(d_out), int(bool(do_dump))), "xeng_corr_run")
+
+    def run_host(self, h_in, h_out, do_dump):
+        """bfXgpuCorrelate(in, out, doDump): host buffers (xgpu_test.py:86-89)."""
+        check(self._lib.xeng_corr_run_host(self._h, ptr(h_in), ptr(h_out), int(bool(do_dump))), "xeng_corr_run_host")
+
+    def accumulate(self, d_in, d_acc, first):
+        """Fused Corr + CorrAcc step: d_acc (=|+=) X(d_in)."""
+        check(self._lib.xeng_corr_accumulate(self._h, ptr(d_in), ptr(d_acc), int(bool(first))), "xeng_corr_accumulate")
+
+    def sync(self):
+        check(self._lib.xeng_corr_sync(self._h), "xeng_corr_sync")
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.xeng_corr_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def get_order(ant_to_input):
+    """bfXgpuGetOrder (corr_block.py:331-333): returns (antpol_to_bl, bl_is_conj) int32 [ns,ns,np,np]."""
+    a2i = np.ascontiguousarray(ant_to_input, dtype=np.int32)
+    nstand, npol = a2i.shape
+    a2bl = np.zeros([nstand, nstand, npol, npol], dtype=np.int32)
+    conj = np.zeros_like(a2bl)
+    check(_lib.load().xeng_get_order(ptr(a2i), ptr(a2bl), ptr(conj), nstand, npol), "xeng_get_order")
+    return a2bl, conj
+
+
+def acc(d_acc, d_in, n, first, stream=None):
+    """BFMap 'a = b' / 'a += b' (corr_acc_block.py:299-306) over n int32 words."""
+    check(_lib.load().xeng_acc(ptr(d_acc), ptr(d_in), int(n), int(bool(first)), ptr(stream)), "xeng_acc")
+
+
+def subsel(d_in, d_out, d_vismap, d_conj, nvis, nchan, nchan_sum, wpc, stream=None):
+    """bfXgpuSubSelect (corr_subsel_block.py:298)."""
+    check(_lib.load().xeng_subsel(ptr(d_in), ptr(d_out), ptr(d_vismap), ptr(d_conj), nvis, nchan, nchan_sum, wpc,
+                                  ptr(stream)), "xeng_subsel")
+
+
+def reorder(d_in, d_out, d_a2bl, d_conj, nstand, npol, nchan, wpc, stream=None):
+    """bfXgpuReorder (corr_output_full_block.py:669), on the device."""
+    check(_lib.load().xeng_reorder(ptr(d_in), ptr(d_out), ptr(d_a2bl), ptr(d_conj), nstand, npol, nchan, wpc,
+                                   ptr(stream)), "xeng_reorder")
+
+
+class Beamformer(object):
+    """bfBeamformInitialize / Run / Integrate / IntegrateSingleBeam
+    (beamform_block.py:251,449; beamform_sum_beams_block.py:245; beamform_sum_single_beam_block.py:114)."""
+
+    def __init__(self, gpu=-1, ninput=704, nchan=192, ntime=480, nbeam=16, ntime_blocks=0, stream=None):
+        self._lib = _lib.load()
+        self._h = C.c_void_p()
+        check(self._lib.xeng_bf_create(C.byref(self._h), gpu, ninput, nchan, ntime, nbeam, ntime_blocks), "xeng_bf_create")
+        self.ninput, self.nchan, self.ntime, self.nbeam = ninput, nchan, ntime, nbeam
+        if stream is not None:
+            self.set_stream(stream)
+
+    def set_stream(self, stream):
+        check(self._lib.xeng_bf_set_stream(self._h, ptr(stream)), "xeng_bf_set_stream")
+
+    def run(self, d_in, d_out, d_weights):
+        check(self._lib.xeng_bf_run(self._h, ptr(d_in), ptr(d_out), ptr(d_weights)), "xeng_bf_run")
+
+    def integrate(self, d_in, d_out, ntime_sum):
+        check(self._lib.xeng_bf_integrate(self._h, ptr(d_in), ptr(d_out), int(ntime_sum)), "xeng_bf_integrate")
+
+    def integrate_single(self, d_in, d_out, ntime_sum, beam_id):
+        check(self._lib.xeng_bf_integrate_single(self._h, ptr(d_in), ptr(d_out), int(ntime_sum), int(beam_id)),
+              "xeng_bf_integrate_single")
+
+    def sync(self):
+        check(self._lib.xeng_bf_sync(self._h), "xeng_bf_sync")
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.xeng_bf_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -34,7 +34,7 @@ int xeng_device_count(void);
 typedef struct xeng_corr_s* xeng_corr_t;
 
 /* Replaces bfXgpuInitialize(in, out, gpu) -- corr_block.py:253.  gpu = -1 keeps the current device.
- * npol must be 2 and nstand even (xGPU register-tile order, corr_block.py:37-58). */
+ * npol must be 2 and nstand a multiple of 4 (xGPU register-tile order, corr_block.py:37-58). */
 int xeng_corr_create(xeng_corr_t* h, int nstand, int npol, int nchan, int ntime_gulp, int gpu);
 int xeng_corr_destroy(xeng_corr_t h);
 int xeng_corr_set_stream(xeng_corr_t h, void* cuda_stream);

@@ -1,0 +1,211 @@
+"""GPU parity of Corr / CorrAcc / CorrSubsel / reorder against the numpy oracle, through the C-ABI.
+Bit-exact (integer work).  Mirrors pipeline/verification/xgpu_test.py and Corr._compare of the reference."""
+import numpy as np
+import pytest
+
+from oracle import xeng_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.fail("gpu-marked test run without a CUDA device")
+    return torch
+
+
+def _voltages(rng, nt, nchan, nstand, npol=2, edge=True):
+    v = rng.integers(0, 256, size=(nt, nchan, nstand, npol), dtype=np.uint8)
+    if edge and v.size >= 8:  # bytes randint(0,255) never yields + the -8 corner cases
+        flat = v.reshape(-1)
+        flat[:8] = [0xFF, 0x88, 0x80, 0x08, 0x00, 0x77, 0x78, 0x87]
+        flat[-4:] = [0x88, 0x88, 0xFF, 0x80]
+    return v
+
+
+def _run_corr(torch, v, impl=0, ngulp=1):
+    from xengine import ops
+    nt, nchan, nstand, npol = v.shape
+    nt_g = nt // ngulp
+    xc = ops.XCorr(nstand=nstand, npol=npol, nchan=nchan, ntime_gulp=nt_g)
+    xc.set_impl(impl)
+    out = torch.full((2, nchan, ops.words_per_chan(nstand)), -12345, dtype=torch.int32, device="cuda")
+    for g in range(ngulp):
+        d_in = torch.from_numpy(np.ascontiguousarray(v[g * nt_g:(g + 1) * nt_g])).cuda()
+        xc.run(d_in, out, g == ngulp - 1)
+        xc.sync()
+    res = out.cpu().numpy()
+    xc.close()
+    return res
+
+
+@pytest.mark.parametrize("impl", [1, 0])
+@pytest.mark.parametrize("shape", [
+    (16, 2, 4), (37, 3, 8), (32, 1, 64), (50, 3, 68), (480, 2, 352), (96, 5, 128), (17, 2, 12),
+])
+def test_corr_matches_oracle(torch_cuda, impl, shape):
+    nt, nchan, nstand = shape
+    rng = np.random.default_rng(1234 + nt + nstand)
+    v = _voltages(rng, nt, nchan, nstand)
+    got = _run_corr(torch_cuda, v, impl=impl)
+    want = orc.corr_xgpu(v)
+    assert got.dtype == np.int32 and got.shape == want.shape
+    assert np.array_equal(got, want)
+
+
+def test_corr_extreme_values(torch_cuda):
+    """All inputs -8-8j: every product is 128, the largest magnitude; and all-zero input."""
+    v = np.full((480, 2, 352, 2), 0x88, dtype=np.uint8)
+    got = _run_corr(torch_cuda, v)
+    want = orc.corr_xgpu(v)
+    assert np.array_equal(got, want) and got.max() == 128 * 480
+    v[:] = 0
+    assert not _run_corr(torch_cuda, v).any()
+
+
+@pytest.mark.parametrize("impl", [1, 0])
+def test_corr_multi_gulp_dump_and_clear(torch_cuda, impl):
+    """xGPU semantics (corr_block.py:445): integrate over calls, write on doDump, clear afterwards."""
+    from xengine import ops
+    torch = torch_cuda
+    rng = np.random.default_rng(7)
+    nt, nchan, nstand = 48, 3, 36
+    xc = ops.XCorr(nstand=nstand, nchan=nchan, ntime_gulp=nt)
+    xc.set_impl(impl)
+    out = torch.zeros((2, nchan, ops.words_per_chan(nstand)), dtype=torch.int32, device="cuda")
+    for integ, ngulp in enumerate([3, 1, 2]):
+        want = np.zeros(out.shape, dtype=np.int64)
+        out.fill_(-1)
+        for g in range(ngulp):
+            v = _voltages(rng, nt, nchan, nstand)
+            want += orc.corr_xgpu(v)
+            xc.run(torch.from_numpy(v).cuda(), out, g == ngulp - 1)
+            xc.sync()
+            if g < ngulp - 1:
+                assert int(out.min()) == -1 and int(out.max()) == -1   # untouched until doDump
+        assert np.array_equal(out.cpu().numpy(), want.astype(np.int32)), "integration %d" % integ
+    xc.close()
+
+
+def test_corr_fused_accumulate(torch_cuda):
+    """Fused Corr+CorrAcc (bulk-reduce epilogue) == oracle corr followed by corr_acc."""
+    from xengine import ops
+    torch = torch_cuda
+    rng = np.random.default_rng(11)
+    nt, nchan, nstand = 480, 2, 352
+    xc = ops.XCorr(nstand=nstand, nchan=nchan, ntime_gulp=nt)
+    acc = torch.full((2, nchan, ops.words_per_chan(nstand)), 99, dtype=torch.int32, device="cuda")
+    want = None
+    for g in range(3):
+        v = _voltages(rng, nt, nchan, nstand)
+        x = orc.corr_xgpu(v)
+        want = orc.corr_acc(x.copy() if want is None else want, x, first=(g == 0))
+        xc.accumulate(torch.from_numpy(v).cuda(), acc, g == 0)
+    xc.sync()
+    assert np.array_equal(acc.cpu().numpy(), want)
+    xc.close()
+
+
+def test_corr_host_variant(torch_cuda):
+    """bfXgpuCorrelate: host buffers in and out (xgpu_test.py:86-89)."""
+    from xengine import ops
+    rng = np.random.default_rng(5)
+    v = _voltages(rng, 64, 2, 16)
+    xc = ops.XCorr(nstand=16, nchan=2, ntime_gulp=64)
+    out = np.zeros((2, 2, ops.words_per_chan(16)), dtype=np.int32)
+    xc.run_host(v, out, True)
+    assert np.array_equal(out, orc.corr_xgpu(v))
+    xc.close()
+
+
+def test_corr_tc_equals_simt_full_size(torch_cuda):
+    """704 inputs x 480 samples, more channels than the oracle is asked to do: tensor-core kernel vs the
+    CUDA-core cross-check kernel on every word, oracle on two channels."""
+    rng = np.random.default_rng(2024)
+    v = _voltages(rng, 480, 24, 352)
+    a = _run_corr(torch_cuda, v, impl=0)
+    b = _run_corr(torch_cuda, v, impl=1)
+    assert np.array_equal(a, b)
+    for c in (0, 23):
+        assert np.array_equal(a[:, c:c + 1], orc.corr_xgpu(v[:, c:c + 1]))
+
+
+def test_corr_linearity_in_time(torch_cuda):
+    """Size-independent property: X(gulp A ++ gulp B) == X(A) + X(B)."""
+    rng = np.random.default_rng(99)
+    v = _voltages(rng, 960, 4, 352)
+    whole = _run_corr(torch_cuda, v, ngulp=1)
+    two = _run_corr(torch_cuda, v, ngulp=2)
+    parts = _run_corr(torch_cuda, v[:480]).astype(np.int64) + _run_corr(torch_cuda, v[480:])
+    assert np.array_equal(whole, two) and np.array_equal(whole, parts.astype(np.int32))
+
+
+def test_get_order_matches_oracle():
+    from xengine import ops
+    for nstand in (4, 12, 352):
+        a2i = np.arange(nstand * 2, dtype=np.int32).reshape(nstand, 2)
+        for perm in (False, True):
+            if perm:
+                a2i = np.random.default_rng(3).permutation(nstand * 2).astype(np.int32).reshape(nstand, 2)
+            a2bl, conj = ops.get_order(a2i)
+            wa, wc = orc.get_order(a2i)
+            assert np.array_equal(a2bl, wa) and np.array_equal(conj, wc)
+
+
+@pytest.mark.parametrize("n", [0, 1, 5, 4096, 1000003])
+def test_acc(torch_cuda, n):
+    from xengine import ops
+    torch = torch_cuda
+    rng = np.random.default_rng(n)
+    a = rng.integers(-2**30, 2**30, size=n, dtype=np.int32)
+    b = rng.integers(-2**30, 2**30, size=n, dtype=np.int32)
+    da, db = torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()
+    if n == 0:
+        da = torch.zeros(4, dtype=torch.int32, device="cuda"); db = da.clone()
+    ops.acc(da, db, n, True)
+    torch.cuda.synchronize()
+    assert np.array_equal(da.cpu().numpy()[:n], b)
+    ops.acc(da, db, n, False)
+    ops.acc(da, db, n, False)
+    torch.cuda.synchronize()
+    assert np.array_equal(da.cpu().numpy()[:n], (3 * b.astype(np.int64)).astype(np.int32))
+
+
+def test_subsel_and_reorder(torch_cuda):
+    from xengine import ops
+    torch = torch_cuda
+    rng = np.random.default_rng(42)
+    nt, nchan, nstand = 40, 8, 12
+    v = _voltages(rng, nt, nchan, nstand)
+    x = _run_corr(torch, v)
+    assert np.array_equal(x, orc.corr_xgpu(v))
+    a2i = np.arange(nstand * 2, dtype=np.int32).reshape(nstand, 2)
+    a2bl, conj = ops.get_order(a2i)
+    # reorder == v(s0,p0) conj(v(s1,p1)) for every pair, which is what make_golden_inputs.py pins
+    dx = torch.from_numpy(x).cuda()
+    out = torch.zeros((nstand, nstand, 2, 2, nchan, 2), dtype=torch.int32, device="cuda")
+    ops.reorder(dx, out, torch.from_numpy(a2bl).cuda(), torch.from_numpy(conj).cuda(), nstand, 2, nchan,
+                ops.words_per_chan(nstand))
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    assert np.array_equal(got, orc.reorder(x, a2bl, conj))
+    fre, fim = orc.corr_full(v)
+    assert np.array_equal(got[..., 0], np.moveaxis(fre, 0, -1))
+    assert np.array_equal(got[..., 1], np.moveaxis(fim, 0, -1))
+    # subselect: random baselines in both station orders, nchan_sum in {1,2,4}
+    bls = [[[int(rng.integers(nstand)), int(rng.integers(2))], [int(rng.integers(nstand)), int(rng.integers(2))]]
+           for _ in range(301)]
+    vm, cj = orc.baselines_to_vismap(bls, a2bl, conj)
+    for ncs in (1, 2, 4):
+        o = torch.zeros((nchan // ncs, len(bls), 2), dtype=torch.int32, device="cuda")
+        ops.subsel(dx, o, torch.from_numpy(vm).cuda(), torch.from_numpy(cj).cuda(), len(bls), nchan, ncs,
+                   ops.words_per_chan(nstand))
+        torch.cuda.synchronize()
+        got = o.cpu().numpy()
+        assert np.array_equal(got, orc.subselect(x, vm, cj, ncs))
+        # test_corr_part_rx.py:76-84: equals the channel-summed logical visibility
+        for k, ((s0, p0), (s1, p1)) in enumerate(bls[:50]):
+            assert np.array_equal(got[:, k, 0], fre[:, s0, s1, p0, p1].reshape(-1, ncs).sum(1))
+            assert np.array_equal(got[:, k, 1], fim[:, s0, s1, p0, p1].reshape(-1, ncs).sum(1))
