@@ -1,0 +1,15 @@
+#!/bin/bash
+# Round routine on the GPU box: tests, smoke, bench, ncu launch list + full capture of the top kernel.
+set -u
+TAG=${1:-r01}
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -x -q -m gpu > gpurun_out/${TAG}_pytest.log 2>&1; echo "pytest rc=$?" 
+timeout 300 python __graft_entry__.py smoke > gpurun_out/${TAG}_smoke.log 2>&1; echo "smoke rc=$?"
+timeout 600 python bench.py > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err; echo "bench rc=$?"
+SHORT="python bench.py --steps 4 --warmup 3 --no-cpu-baseline"
+timeout 300 $SHORT > gpurun_out/${TAG}_plain.log 2>&1 && \
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
+    --log-file gpurun_out/${TAG}_launches.csv $SHORT > gpurun_out/${TAG}_ncu1.log 2>&1; echo "ncu list rc=$?"
+timeout 300 $SHORT > gpurun_out/${TAG}_plain2.log 2>&1 && \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:corr_tc -s 3 -c 2 \
+    -f -o gpurun_out/${TAG}_corr $SHORT > gpurun_out/${TAG}_ncu2.log 2>&1; echo "ncu full rc=$?"
