@@ -20,6 +20,9 @@ struct CorrArgs {
 int corr_tc_smem_bytes();
 cudaError_t launch_corr_tc(const CorrArgs& a, int nsm, cudaStream_t stream);
 cudaError_t launch_corr_simt(const CorrArgs& a, cudaStream_t stream);
+// TMA-fed tensor-core kernel (xeng_corr2.cu): needs ninput % 16 == 0 and 16-byte aligned buffers
+bool corr_tma_supported(const CorrArgs& a);
+cudaError_t launch_corr_tma(const CorrArgs& a, int nsm, cudaStream_t stream);
 
 // bandwidth kernels (xeng_vis.cu)
 cudaError_t launch_acc(int32_t* acc, const int32_t* in, size_t n, int first, cudaStream_t stream);
