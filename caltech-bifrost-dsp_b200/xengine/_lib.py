@@ -45,6 +45,8 @@ SIGNATURES = {
     "xeng_bf_run": (_i, [_vp, _vp, _vp, _vp]),
     "xeng_bf_integrate": (_i, [_vp, _vp, _vp, _i]),
     "xeng_bf_integrate_single": (_i, [_vp, _vp, _vp, _i, _i]),
+    "xeng_bf_run_integrate": (_i, [_vp, _vp, _vp, _vp, _i]),
+    "xeng_bf_voltages": (_vp, [_vp]),
     "xeng_bf_sync": (_i, [_vp]),
 }
 

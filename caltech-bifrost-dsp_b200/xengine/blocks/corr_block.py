@@ -1,0 +1,202 @@
+"""Corr: cross-correlate 4+4-bit voltages on the B200 tensor cores, output in xGPU's triangular order.
+
+Drop-in for ``lwa352_pipeline.blocks.corr_block.Corr`` (reference: pipeline/lwa352_pipeline/blocks/
+corr_block.py:60-472): same constructor signature, command keys (``start_time``, ``acc_len``), ring header
+keys and output byte layout.  Where the reference calls ``_bf.bfXgpuInitialize`` / ``bfXgpuKernel`` /
+``bfXgpuGetOrder`` (corr_block.py:253,445,331) this block calls libxeng through ``xengine.ops``.
+
+Differences that do not change the data products:
+  * the integration is accumulated straight into the reserved output span (``xeng_corr_accumulate``), so there
+    is no library-internal accumulator to go stale when an input sequence ends mid-integration;
+  * ``acc_len = 0`` stops cleanly (the reference falls through to ``WriteSpan(None.ring, ...)``,
+    corr_block.py:421-435);
+  * ``test=True`` cross-checks every dump on the GPU against the independent CUDA-core kernel instead of running
+    numpy for ~10 minutes per gulp (corr_block.py:265-315).
+"""
+import json
+import time
+
+import numpy as np
+
+from .. import ops
+from .. import runtime as rt
+from ._integration import IntegrationClock
+from .block_base import Block
+
+
+def tri_index(i, j):
+    """Index into a lower-triangular matrix stored row by row (corr_block.py:27-35)."""
+    return (i * (i + 1)) // 2 + j
+
+
+def regtile_index(in0, in1, nstand):
+    """Word index of the product of inputs ``in0`` and ``in1`` (stand of in1 >= stand of in0) inside one channel of
+    the xGPU register-tile-order buffer (corr_block.py:37-58)."""
+    a0, a1, p0, p1 = in0 >> 1, in1 >> 1, in0 & 1, in1 & 1
+    quadrant = 2 * (a0 & 1) + (a1 & 1)
+    cells_per_quadrant = (nstand // 2 + 1) * nstand // 4
+    cell = quadrant * cells_per_quadrant + tri_index(a1 // 2, a0 // 2)
+    return 4 * cell + 2 * p1 + p0
+
+
+class Corr(Block):
+    def __init__(self, log, iring, oring, ntime_gulp=2500, guarantee=True, core=-1, nchan=192, npol=2, nstand=352,
+                 acc_len=2400, gpu=-1, test=False, etcd_client=None, autostartat=0, ant_to_input=None):
+        assert (acc_len % ntime_gulp == 0), "Acculmulation length must be a multiple of gulp size"
+        super(Corr, self).__init__(log, iring, oring, guarantee, core, etcd_client=etcd_client)
+        self.ntime_gulp, self.nchan, self.npol, self.nstand = ntime_gulp, nchan, npol, nstand
+        self.matlen = nchan * (nstand // 2 + 1) * (nstand // 4) * npol * npol * 4
+        self.gpu = gpu
+        self.test = test
+        rt.set_device(self.gpu)
+
+        self.size_proclog.update({'nseq_per_gulp': self.ntime_gulp})
+        self.igulp_size = self.ntime_gulp * nchan * nstand * npol      # one byte per 4+4-bit sample
+        self.ogulp_size = self.matlen * 8                              # int32 real plane + int32 imaginary plane
+
+        self.define_command_key('start_time', type=int, initial_val=autostartat,
+                                condition=lambda x: (x == -1) or (x % self.ntime_gulp == 0))
+        self.define_command_key('acc_len', type=int, initial_val=acc_len,
+                                condition=lambda x: x % self.ntime_gulp == 0)
+        self.update_stats({'xgpu_acc_len': self.ntime_gulp})
+
+        try:
+            self._xcorr = ops.XCorr(nstand=nstand, npol=npol, nchan=nchan, ntime_gulp=ntime_gulp, gpu=gpu)
+        except Exception as e:
+            self.log.error("xeng_corr_create failed: %s" % e)
+            raise RuntimeError(str(e))
+        assert self._xcorr.matlen == self.matlen
+        self._xcheck = None     # CUDA-core cross-check engine, created on first use when test=True
+
+        self.antpol_to_input = np.zeros([nstand, npol], dtype=np.int32)
+        self.antpol_to_bl = np.zeros([nstand, nstand, npol, npol], dtype=np.int32)
+        self.bl_is_conj = np.zeros([nstand, nstand, npol, npol], dtype=np.int32)
+        if ant_to_input is not None:
+            self.update_baseline_indices(ant_to_input)
+
+    def update_baseline_indices(self, ant_to_input):
+        """Fill ``antpol_to_bl`` / ``bl_is_conj`` ([nstand, nstand, npol, npol]) from a [nstand, npol] map of
+        correlator input numbers: the word index inside one channel of the output buffer that holds the product
+        of (stand0, pol0) and (stand1, pol1), and whether it must be conjugated to read as
+        ``v(s0,p0) conj(v(s1,p1))``.  In place, so downstream blocks constructed with these arrays see updates."""
+        rt.set_core(self.core)
+        self.antpol_to_input[...] = ant_to_input
+        a2bl, conj = ops.get_order(self.antpol_to_input)
+        self.antpol_to_bl[...] = a2bl
+        self.bl_is_conj[...] = conj
+
+    # ------------------------------------------------------------------ test mode
+    def _crosscheck_gulp(self, idata, first):
+        """test=True: repeat the gulp on the CUDA-core kernel into a private accumulator."""
+        if self._xcheck is None:
+            self._xcheck = ops.XCorr(nstand=self.nstand, npol=self.npol, nchan=self.nchan,
+                                     ntime_gulp=self.ntime_gulp, gpu=self.gpu)
+            self._xcheck.set_impl(1)
+            self._xcheck_acc = rt.zeros(2 * self.matlen, 'i32', 'cuda')
+        self._xcheck.accumulate(idata, self._xcheck_acc, first)
+
+    def _crosscheck_compare(self, odata):
+        import torch
+        self._xcheck.sync()
+        got = odata.view(torch.int32) if isinstance(odata, torch.Tensor) else torch.as_tensor(odata).view(torch.int32)
+        ok = bool(torch.equal(got.reshape(-1), self._xcheck_acc.reshape(-1)))
+        self.update_stats({'test_match': ok})
+        (self.log.info if ok else self.log.error)("CORR >> tensor-core vs CUDA-core dump match: %s" % ok)
+        return ok
+
+    # ------------------------------------------------------------------ main loop
+    def main(self):
+        rt.set_core(self.core)
+        rt.set_device(self.gpu)
+        self.bind_proclog.update({'ncore': 1, 'core0': rt.get_core()})
+        self.oring.resize(self.ogulp_size)
+        step = self.ntime_gulp
+        clock = IntegrationClock(recover_skip=10, asap="boundary")
+        time_tag = 1
+        self.update_stats({'state': 'starting'})
+        with self.oring.begin_writing() as oring:
+            prev = time.time()
+            self.update_pending = True          # load the constructor's start_time / acc_len on the first gulp
+            oseq = ospan = None
+            for iseq in self.iring.read(guarantee=self.guarantee):
+                self.log.info('CORR >> new input sequence!')
+                ihdr = json.loads(iseq.header.tostring())
+                now = ihdr['seq0']
+                ohdr = dict(ihdr)
+                # the output is xGPU-ordered, not [stand, pol]: the input maps do not describe it
+                ohdr.pop('ant_to_input', None)
+                ohdr.pop('input_to_ant', None)
+                if clock.resequence(now):
+                    self.log.info("CORR >> Recovering start time set to %d. Accumulating %d samples"
+                                  % (clock.start_time, clock.acc_len))
+                    ohdr['acc_len'], ohdr['seq0'] = clock.acc_len, clock.start_time
+                self.sequence_proclog.update(ohdr)
+                ospan = None                    # an integration cut short by the end of a sequence is dropped
+                process_time = acquire_time = reserve_time = 0.
+                for ispan in iseq.read(self.igulp_size):
+                    if ispan.size < self.igulp_size:
+                        self.log.info("CORR >>> Ignoring final gulp (expected %d bytes but got %d)"
+                                      % (self.igulp_size, ispan.size))
+                        continue
+                    if self.update_pending:
+                        self.update_command_vals()
+                        clock.retarget(self.command_vals['start_time'], self.command_vals['acc_len'], now)
+                        self.log.info("CORR >> New start time set to %d. Accumulating %d samples"
+                                      % (clock.start_time, clock.acc_len))
+                        ohdr['acc_len'], ohdr['seq0'] = clock.acc_len, clock.start_time
+                    self.update_stats({'curr_sample': now})
+                    if clock.acc_len == 0:      # stop condition
+                        self.update_stats({'state': 'stopped'})
+                        if oseq:
+                            oseq.end()
+                        oseq = ospan = None
+                        clock.stop()
+                        now += step
+                        continue
+                    if clock.begins(now, step):
+                        self.log.info("CORR >> Start time %d reached." % clock.start_time)
+                        if oseq:
+                            oseq.end()
+                        self.sequence_proclog.update(ohdr)
+                        oseq = oring.begin_sequence(time_tag=time_tag, header=json.dumps(ohdr),
+                                                    nringlet=iseq.nringlet)
+                        time_tag += 1
+                    if not clock.running:
+                        self.update_stats({'state': 'waiting'})
+                        now += step
+                        continue
+                    self.update_stats({'state': 'running'})
+                    t = time.time()
+                    acquire_time, prev = t - prev, t
+                    is_first, is_last = (now == clock.first), (now == clock.last)
+                    if is_first:
+                        ospan = rt.WriteSpan(oseq.ring, self.ogulp_size, nonblocking=False)
+                        t = time.time()
+                        reserve_time, prev = t - prev, t
+                    if ospan is None:
+                        self.log.error("CORR: trying to write to not-yet-opened ospan")
+                        now += step
+                        continue
+                    # device boundary (replaces _bf.bfXgpuKernel, corr_block.py:445): ospan (+)= X(ispan)
+                    self._xcorr.accumulate(ispan.data, ospan.data, is_first)
+                    if self.test:
+                        self._crosscheck_gulp(ispan.data, is_first)
+                    self._xcorr.sync()          # the input span may be released when this iteration ends
+                    t = time.time()
+                    process_time += t - prev
+                    prev = t
+                    if is_last:
+                        if self.test:
+                            self._crosscheck_compare(ospan.data)
+                        ospan.close()
+                        ospan = None
+                        gbps = 8 * clock.acc_len * ihdr['nchan'] * ihdr['nstand'] * ihdr['npol'] / process_time / 1e9
+                        self.perf_proclog.update({'acquire_time': acquire_time, 'reserve_time': reserve_time,
+                                                  'process_time': process_time, 'gbps': gbps})
+                        self.update_stats({'last_end_sample': now, 'throughput': gbps})
+                        process_time = 0.
+                        clock.advance(step)
+                    now += step
+                if oseq:
+                    oseq.end()
+                oseq = None

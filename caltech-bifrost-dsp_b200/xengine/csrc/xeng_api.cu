@@ -57,6 +57,7 @@ struct xeng_corr_s {
 struct xeng_bf_s {
   int device, ninput, nchan, ntime, nbeam, ntime_blocks;
   cudaStream_t stream;
+  float2* d_volt;   // scratch voltage beams for xeng_bf_run_integrate
 };
 
 extern "C" {
@@ -266,6 +267,7 @@ int xeng_bf_create(xeng_bf_t* out, int gpu, int ninput, int nchan, int ntime, in
   if (!h) return fail(XENG_ERR_NOMEM, "host allocation failed");
   h->ninput = ninput; h->nchan = nchan; h->ntime = ntime; h->nbeam = nbeam; h->ntime_blocks = ntime_blocks;
   h->stream = nullptr;
+  h->d_volt = nullptr;
   cudaError_t e = cudaGetDevice(&h->device);
   if (e != cudaSuccess) {
     delete h;
@@ -275,6 +277,10 @@ int xeng_bf_create(xeng_bf_t* out, int gpu, int ninput, int nchan, int ntime, in
   return XENG_OK;
 }
 int xeng_bf_destroy(xeng_bf_t h) {
+  if (h && h->d_volt) {
+    cudaSetDevice(h->device);
+    cudaFree(h->d_volt);
+  }
   delete h;
   return XENG_OK;
 }
@@ -295,6 +301,17 @@ int xeng_bf_run(xeng_bf_t h, const void* d_in, void* d_out, const void* d_w) {
   XENG_CUDA(xeng::launch_beamform(a, h->stream));
   return XENG_OK;
 }
+
+int xeng_bf_run_integrate(xeng_bf_t h, const void* d_in, void* d_out, const void* d_w, int ntime_sum) {
+  if (!h || !d_in || !d_out || !d_w) return fail(XENG_ERR_ARG, "null pointer");
+  if (ntime_sum <= 0 || (h->nbeam & 1) || h->ntime % ntime_sum) return fail(XENG_ERR_ARG, "need ntime_sum | ntime and an even number of beams");
+  XENG_CUDA(cudaSetDevice(h->device));
+  if (!h->d_volt) XENG_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->d_volt), sizeof(float2) * h->nchan * h->nbeam * static_cast<size_t>(h->ntime)));
+  int rc = xeng_bf_run(h, d_in, h->d_volt, d_w);
+  if (rc) return rc;
+  return xeng_bf_integrate(h, h->d_volt, d_out, ntime_sum);
+}
+const void* xeng_bf_voltages(xeng_bf_t h) { return h ? h->d_volt : nullptr; }
 
 int xeng_bf_integrate(xeng_bf_t h, const void* d_in, void* d_out, int ntime_sum) {
   if (!h || !d_in || !d_out) return fail(XENG_ERR_ARG, "null pointer");

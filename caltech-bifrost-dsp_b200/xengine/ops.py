@@ -106,6 +106,11 @@ class Beamformer(object):
     def run(self, d_in, d_out, d_weights):
         check(self._lib.xeng_bf_run(self._h, ptr(d_in), ptr(d_out), ptr(d_weights)), "xeng_bf_run")
 
+    def run_integrate(self, d_in, d_out, d_weights, ntime_sum):
+        """Beamform's ntime_sum mode: voltages stay in the handle, integrated powers go to d_out."""
+        check(self._lib.xeng_bf_run_integrate(self._h, ptr(d_in), ptr(d_out), ptr(d_weights), int(ntime_sum)),
+              "xeng_bf_run_integrate")
+
     def integrate(self, d_in, d_out, ntime_sum):
         check(self._lib.xeng_bf_integrate(self._h, ptr(d_in), ptr(d_out), int(ntime_sum)), "xeng_bf_integrate")
 

@@ -98,6 +98,13 @@ int xeng_bf_integrate(xeng_bf_t h, const void* d_in, void* d_out, int ntime_sum)
 /* Replaces bfBeamformIntegrateSingleBeam(in, out, ntime_sum, beam_id) -- beamform_sum_single_beam_block.py:114.
  * d_out f32 [ntime/ntime_sum][nchan][4] for dual-pol beam beam_id. */
 int xeng_bf_integrate_single(xeng_bf_t h, const void* d_in, void* d_out, int ntime_sum, int beam_id);
+/* Beamform's ntime_sum != None mode (beamform_block.py:216-218,249-251: bfBeamformInitialize with ntime_blocks > 0,
+ * then bfBeamformRun emits integrated powers): d_out f32 [nbeam/2][ntime/ntime_sum][nchan][4]; the voltage beams
+ * stay in a handle-owned scratch buffer (also readable through xeng_bf_voltages for a VLBI-style tap). */
+int xeng_bf_run_integrate(xeng_bf_t h, const void* d_in, void* d_out, const void* d_weights, int ntime_sum);
+/* Device pointer of the handle-owned cf32 [nchan][nbeam][ntime] voltage scratch (NULL before the first
+ * xeng_bf_run_integrate). */
+const void* xeng_bf_voltages(xeng_bf_t h);
 int xeng_bf_sync(xeng_bf_t h);
 
 #ifdef __cplusplus

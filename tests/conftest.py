@@ -19,3 +19,28 @@ def pytest_configure(config):
 @pytest.fixture(scope="session")
 def golden_dir():
     return GOLDEN
+
+
+@pytest.fixture
+def host_only(monkeypatch):
+    """Run the blocks' host logic without a GPU: libxeng entry points are replaced by the tag-moving doubles of
+    tests/fakes.py and 'cuda' allocations land in host memory.  Only for `-m "not gpu"` tests of state machines,
+    headers and command handling; the kernels themselves are covered by the gpu tests."""
+    import fakes
+    from xengine import ops, ringshim
+    from xengine import runtime as rt
+
+    real_alloc = ringshim.alloc_bytes
+
+    def host_alloc(nbytes, space):
+        return real_alloc(nbytes, "system" if space == "cuda" else space)
+
+    monkeypatch.setattr(ringshim, "alloc_bytes", host_alloc)
+    monkeypatch.setattr(rt, "alloc_bytes", host_alloc)
+    monkeypatch.setattr(rt, "set_device", lambda gpu: None)
+    monkeypatch.setattr(ops, "XCorr", fakes.FakeXCorr)
+    monkeypatch.setattr(ops, "acc", fakes.fake_acc)
+    monkeypatch.setattr(ops, "subsel", fakes.fake_subsel)
+    monkeypatch.setattr(ops, "Beamformer", fakes.FakeBeamformer)
+    del fakes.CALLS[:]
+    return fakes
