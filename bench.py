@@ -180,7 +180,7 @@ class ClockSampler(object):
 def run_b200(args):
     import torch
     import torch.distributed as dist
-    from xengine import ops
+    from xengine import ops, sharding
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the B200 arm has no CPU fallback (use --impl reference)")
@@ -220,7 +220,7 @@ def run_b200(args):
     def dump_device():
         d_dump.copy_(d_acc, non_blocking=True)             # CorrAcc's copy_array into its output span
         if world > 1:
-            dist.gather(d_dump, gather_list, dst=0)
+            sharding.gather_to_root(d_dump, dist, root=0, out=gather_list)
 
     def step_device(i):
         xc.accumulate(d_in[i % NBUF], d_acc, (i % accg) == 0)

@@ -1,0 +1,59 @@
+"""Channel-slab sharding of the X-engine across GPUs (one process per GPU).
+
+Every product of the path (visibility, sub-selected visibility, beam sample, beam power) is per frequency channel,
+and CorrSubsel's channel sums stay inside a slab, so ranks never exchange data on the hot path.  The reference
+deploys the same way: one independent pipeline process per sub-band (pipeline/scripts/lwa352-start-pipeline.sh:1-31;
+header keys as written by capture_block.py:264-280).  The only communication is the gather of finished products to
+rank 0, which stands where the reference sends UDP packets to a central receiver.
+"""
+CHAN_BW_HZ = 23925.78125          # 196 MHz / 8192 (capture_block.py:165)
+
+
+def slab(rank, world_size, system_nchan):
+    """Contiguous channel slab of ``rank``: (chan0, nchan).  ``system_nchan`` must divide evenly."""
+    if world_size <= 0 or not (0 <= rank < world_size):
+        raise ValueError("bad rank %r / world size %r" % (rank, world_size))
+    if system_nchan % world_size:
+        raise ValueError("%d channels do not split evenly over %d ranks" % (system_nchan, world_size))
+    nchan = system_nchan // world_size
+    return rank * nchan, nchan
+
+
+def slab_header(base_header, rank, world_size, system_nchan, band_chan0=0):
+    """Sequence header of rank's slab: ``chan0``, ``nchan``, ``system_nchan``, ``sfreq``, ``bw_hz``, ``pipeline_id``."""
+    chan0, nchan = slab(rank, world_size, system_nchan)
+    h = dict(base_header)
+    h.update({'chan0': band_chan0 + chan0, 'nchan': nchan, 'system_nchan': system_nchan,
+              'sfreq': (band_chan0 + chan0) * CHAN_BW_HZ, 'bw_hz': nchan * CHAN_BW_HZ, 'pipeline_id': rank})
+    return h
+
+
+def slab_of(array, rank, world_size, axis=0):
+    """This rank's channels of a full-band array (beam weights [chan, beam, input], calibration tables, ...)."""
+    chan0, nchan = slab(rank, world_size, array.shape[axis])
+    index = [slice(None)] * array.ndim
+    index[axis] = slice(chan0, chan0 + nchan)
+    return array[tuple(index)]
+
+
+def gather_to_root(tensor, dist, root=0, out=None):
+    """Gather every rank's product (same shape on all ranks) to ``root``; returns the list ordered by rank (i.e. by
+    channel slab) on root, None elsewhere.  ``dist`` is torch.distributed (NCCL over NVLink on GPUs, gloo in the
+    CPU tests).  ``out``: optional pre-allocated receive list on root, ``out[root]`` may alias ``tensor``."""
+    world = dist.get_world_size()
+    if world == 1:
+        return [tensor]
+    if dist.get_rank() == root:
+        if out is None:
+            out = [tensor if r == root else tensor.new_empty(tensor.shape) for r in range(world)]
+        dist.gather(tensor, out, dst=root)
+        return out
+    dist.gather(tensor, None, dst=root)
+    return None
+
+
+def assemble_visibilities(parts):
+    """Rank-ordered list of slab buffers int32 [2][nchan_slab][W] -> full band [2][nchan_total][W] (a view-level
+    concatenation along channel; used by rank 0 after gather_to_root)."""
+    import torch
+    return torch.cat(list(parts), dim=1)

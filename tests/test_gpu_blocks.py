@@ -1,0 +1,187 @@
+"""End-to-end parity of the block graph on the GPU, in the style of the reference's pipeline test scripts
+(verification/tests/correlator/test_pipeline.sh -> lwa352-pipeline.py --fakesource; verification/tests/
+beamformer/beamformer_test.py, beamformer_sum_test.py): a source thread writes 4+4-bit voltages into the
+``gpu-input`` ring, every block runs ``main()`` on its own thread, the sinks compare with the numpy oracle.
+
+    gpu-input -> Corr -> corr-output -+-> CorrAcc    -> corr-slow-output (cuda_host)
+                                      +-> CorrSubsel -> corr-fast-output (cuda_host)
+    gpu-input -> Beamform -> bf-output -> BeamformSumBeams -> bf-pow-output (cuda_host)
+
+Integer products must be bit-exact; beam voltages / powers within 1e-5 relative (north_star).
+"""
+import json
+import logging
+import threading
+
+import numpy as np
+import pytest
+
+from oracle import xeng_oracle as orc
+
+pytestmark = pytest.mark.gpu
+LOG = logging.getLogger("test")
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.fail("gpu-marked test run without a CUDA device")
+    return torch
+
+
+def header(nchan, nstand, npol, seq0=0):
+    return {'seq0': seq0, 'nchan': nchan, 'nstand': nstand, 'npol': npol, 'sfreq': 40.0e6, 'bw_hz': 23925.78125 * nchan,
+            'chan0': 1672, 'fs_hz': 196000000, 'system_nchan': 3072, 'sync_time': 1, 'pipeline_id': 0,
+            'ant_to_input': np.arange(nstand * npol).reshape(nstand, npol).tolist(),
+            'input_to_ant': [[i // npol, i % npol] for i in range(nstand * npol)]}
+
+
+def source(ring, hdr, gulps):
+    """DummySource stand-in (dummy_source_block.py:221-262): one sequence, one span per gulp."""
+    def run():
+        with ring.begin_writing() as w:
+            with w.begin_sequence(time_tag=0, header=json.dumps(hdr)) as seq:
+                for g in gulps:
+                    with seq.reserve(g.size) as span:
+                        import torch
+                        span.data.copy_(torch.from_numpy(np.ascontiguousarray(g).reshape(-1)))
+    return threading.Thread(target=run, name="source")
+
+
+def sink(ring, gulp, store):
+    def run():
+        for seq in ring.read(guarantee=True):
+            hdr = json.loads(seq.header.tostring())
+            spans = []
+            for sp in seq.read(gulp):
+                d = sp.data
+                spans.append(d.cpu().numpy().copy() if hasattr(d, "cpu") else np.array(d))
+            store.append((hdr, spans))
+    return threading.Thread(target=run, name="sink-" + ring.name)
+
+
+def run_all(threads, timeout=120):
+    errors = []
+
+    def guard(t):
+        fn = t.run
+
+        def wrapped():
+            try:
+                fn()
+            except BaseException as e:          # surface exceptions of block threads in the test
+                errors.append((t.name, repr(e)))
+                raise
+        t.run = wrapped
+    for t in threads:
+        guard(t)
+        t.daemon = True
+        t.start()
+    for t in threads:
+        t.join(timeout)
+    assert not errors, errors
+    assert not [t.name for t in threads if t.is_alive()], "pipeline did not drain"
+
+
+def test_correlator_graph_matches_oracle(torch_cuda):
+    from xengine import ringshim
+    from xengine.blocks import Corr, CorrAcc, CorrSubsel
+    nstand, npol, nchan, nt = 32, 2, 8, 32
+    corr_acc_len, long_acc_len, ngulp = 2 * nt, 4 * nt, 13
+    rng = np.random.default_rng(0xdeadbeef)
+    v = rng.integers(0, 256, size=(ngulp, nt, nchan, nstand, npol), dtype=np.uint8)
+    v[0].reshape(-1)[:4] = [0x88, 0x80, 0x08, 0xFF]
+    r_in = ringshim.Ring("gpu-input", space="cuda")
+    r_corr = ringshim.Ring("corr-output", space="cuda")
+    r_slow = ringshim.Ring("corr-slow-output", space="cuda_host")
+    r_fast = ringshim.Ring("corr-fast-output", space="cuda_host")
+    hdr = header(nchan, nstand, npol)
+    corr = Corr(LOG, r_in, r_corr, ntime_gulp=nt, nchan=nchan, npol=npol, nstand=nstand, acc_len=corr_acc_len,
+                gpu=0, test=True, autostartat=nt, ant_to_input=np.array(hdr['ant_to_input']))
+    acc = CorrAcc(LOG, r_corr, r_slow, nchan=nchan, npol=npol, nstand=nstand, acc_len=long_acc_len, gpu=0,
+                  autostartat=nt + corr_acc_len)
+    sub = CorrSubsel(LOG, r_corr, r_fast, nchan=nchan, npol=npol, nstand=nstand, nchan_sum=4, gpu=0,
+                     antpol_to_bl=corr.antpol_to_bl, bl_is_conj=corr.bl_is_conj)
+    bls = [[[int(a), int(b)], [int(c), int(d)]] for a, b, c, d in
+           zip(rng.integers(0, nstand, sub.nvis_out), rng.integers(0, 2, sub.nvis_out),
+               rng.integers(0, nstand, sub.nvis_out), rng.integers(0, 2, sub.nvis_out))]
+    sub.process_command_strings(json.dumps({"id": "1", "cmd": "update", "val": {"kwargs": {"baselines": bls}}}))
+    slow, fast = [], []
+    run_all([source(r_in, hdr, list(v)), threading.Thread(target=corr.main, name="Corr"),
+             threading.Thread(target=acc.main, name="CorrAcc"), threading.Thread(target=sub.main, name="CorrSubsel"),
+             sink(r_slow, acc.ogulp_size, slow), sink(r_fast, sub.ogulp_size, fast)])
+
+    # Corr integrations: gulps (1,2), (3,4), ... (11,12) -> 6 spans starting at sample nt
+    want_corr = [orc.corr_xgpu(v[1 + 2 * k]) + orc.corr_xgpu(v[2 + 2 * k]) for k in range(6)]
+    assert corr.stats.get('test_match') is True
+    # fast path: every Corr integration, selected baselines, 4-channel sums
+    (fh, fspans), = fast
+    assert fh['nchan'] == nchan // 4 and fh['nvis'] == sub.nvis_out and fh['nchan_sum'] == 4 and fh['baselines'] == bls
+    assert fh['seq0'] == nt and fh['acc_len'] == corr_acc_len
+    vm, cj = orc.baselines_to_vismap(bls, corr.antpol_to_bl, corr.bl_is_conj)
+    assert len(fspans) == 6
+    for k, sp in enumerate(fspans):
+        got = sp.view(np.int32).reshape(nchan // 4, sub.nvis_out, 2)
+        assert np.array_equal(got, orc.subselect(want_corr[k].astype(np.int32), vm, cj, 4)), "fast dump %d" % k
+    # the selected words really are v(s0,p0) conj(v(s1,p1)) summed over time and 4 channels (test_corr_part_rx.py:76-84)
+    parts = [orc.corr_full(v[g]) for g in (1, 2)]
+    full_re, full_im = parts[0][0] + parts[1][0], parts[0][1] + parts[1][1]
+    got0 = fspans[0].view(np.int32).reshape(nchan // 4, sub.nvis_out, 2)
+    for n in (0, 1, 17, sub.nvis_out - 1):
+        (s0, p0), (s1, p1) = bls[n]
+        assert got0[0, n, 0] == full_re[0:4, s0, s1, p0, p1].sum()
+        assert got0[0, n, 1] == full_im[0:4, s0, s1, p0, p1].sum()
+    # slow path: CorrAcc starts at the second Corr integration and sums 2 of them per dump
+    (sh, sspans), = slow
+    assert sh['upstream_acc_len'] == corr_acc_len and sh['acc_len'] == long_acc_len and sh['seq0'] == nt + corr_acc_len
+    assert len(sspans) == 2
+    for k, sp in enumerate(sspans):
+        want = want_corr[1 + 2 * k] + want_corr[2 + 2 * k]
+        assert np.array_equal(sp.view(np.int32).reshape(want.shape), want.astype(np.int32)), "slow dump %d" % k
+
+
+def test_beamformer_graph_matches_oracle(torch_cuda):
+    from xengine import ringshim
+    from xengine.blocks import Beamform, BeamformSumBeams
+    nstand, npol, nchan, nt, nbeam, ntime_sum, ngulp = 40, 2, 16, 120, 8, 24, 3     # beamformer_test.py:18-26 shape
+    ninput = nstand * npol
+    rng = np.random.default_rng(0xaabbccdd)
+    v = rng.integers(0, 255, size=(ngulp, nt, nchan, ninput), dtype=np.uint8)
+    hdr = header(nchan, nstand, npol)
+    freqs = hdr['sfreq'] + (hdr['bw_hz'] / nchan) * np.arange(nchan)
+    cal = ((3 * rng.random((nchan, nbeam, ninput)) + 4) + 1j * (4 * rng.random((nchan, nbeam, ninput)) + 5)).astype(np.complex64)
+    delays = 12 * rng.random((nbeam, ninput))
+    amps = 7 * rng.random((nbeam, ninput)) + 10
+    r_in = ringshim.Ring("gpu-input", space="cuda")
+    r_bf = ringshim.Ring("bf-output", space="cuda")
+    r_pow = ringshim.Ring("bf-pow-output", space="cuda_host")
+    bf = Beamform(LOG, r_in, r_bf, nchan=nchan, nbeam=nbeam, ninput=ninput, ntime_gulp=nt, gpu=0)
+    bfs = BeamformSumBeams(LOG, r_bf, r_pow, nchan=nchan, ntime_gulp=nt, ntime_sum=ntime_sum, gpu=0)
+    bf.freqs = freqs            # commands sent before the first sequence use the block's current frequency axis
+    for b in range(nbeam):      # as BeamformControl does: per-input calibration gains, then delays/amplitudes
+        for i in range(ninput):
+            data = np.stack([cal[:, b, i].real, cal[:, b, i].imag], axis=1).reshape(-1).tolist()
+            bf.process_command_strings(json.dumps({"id": "c", "cmd": "update", "val": {"kwargs": {"coeffs": {
+                "type": "calgains", "input_id": i, "beam_id": b, "data": data}}}}))
+        bf.process_command_strings(json.dumps({"id": "b", "cmd": "update", "val": {"kwargs": {"coeffs": {
+            "type": "beamcoeffs", "beam_id": b, "data": {"delays": delays[b].tolist(), "amps": amps[b].tolist()}}}}}))
+    volts, pows = [], []
+    # the voltage sink is a second reader of bf-output (the position of the reference's VLBI tap)
+    run_all([source(r_in, hdr, list(v)), threading.Thread(target=bf.main, name="Beamform"),
+             threading.Thread(target=bfs.main, name="BeamformSumBeams"),
+             sink(r_bf, nt * nchan * nbeam * 8, volts), sink(r_pow, (nt // ntime_sum) * nchan * (nbeam // 2) * 16, pows)])
+    w = np.stack([orc.beam_weights(freqs, delays[b], amps[b], cal[:, b, :]) for b in range(nbeam)], axis=1)
+    assert np.allclose(bf.gains_cpu, w.astype(np.complex64), rtol=1e-6)
+    (vh, vspans), = volts
+    (ph, pspans), = pows
+    assert (vh['nbeam'], vh['nstand'], vh['npol'], vh['nbit'], vh['complex']) == (nbeam, nbeam, 1, 32, True)
+    assert (ph['nbeam'], ph['npol'], ph['acc_len']) == (nbeam // 2, 2, ntime_sum)
+    assert len(vspans) == ngulp and len(pspans) == ngulp
+    for g in range(ngulp):
+        want_v = orc.beamform(v[g], bf.gains_cpu)
+        got_v = vspans[g].view(np.complex64).reshape(nchan, nbeam, nt)
+        assert np.abs(got_v - want_v).max() / np.abs(want_v).max() <= 1e-5
+        want_p = orc.beam_power_sum(want_v, ntime_sum)
+        got_p = pspans[g].view(np.float32).reshape(nbeam // 2, nt // ntime_sum, nchan, 4)
+        assert np.abs(got_p - want_p).max() / np.abs(want_p).max() <= 1e-5
