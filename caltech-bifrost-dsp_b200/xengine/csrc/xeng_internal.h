@@ -13,6 +13,7 @@ struct CorrArgs {
   int npairs;           // nstand / 2 (station pairs)
   int tiles_per_chan, ntiles;
   int accumulate;       // 0: out = X, 1: out += X
+  int ablate;           // profiling ablation mask (XENG_CORR_ABLATE, results invalid when != 0)
   long words_per_chan;  // (nstand/2+1)*(nstand/4)*16
   long quad_cells;      // (nstand/2+1)*(nstand/4): cells per xGPU quadrant
 };
@@ -23,6 +24,8 @@ cudaError_t launch_corr_simt(const CorrArgs& a, cudaStream_t stream);
 // TMA-fed tensor-core kernel (xeng_corr2.cu): needs ninput % 16 == 0 and 16-byte aligned buffers
 bool corr_tma_supported(const CorrArgs& a);
 cudaError_t launch_corr_tma(const CorrArgs& a, int nsm, cudaStream_t stream);
+// plane-split TMA-fed tensor-core kernel (xeng_corr3.cu): same requirements as the TMA kernel; the default
+cudaError_t launch_corr_planes(const CorrArgs& a, int nsm, cudaStream_t stream);
 
 // bandwidth kernels (xeng_vis.cu)
 cudaError_t launch_acc(int32_t* acc, const int32_t* in, size_t n, int first, cudaStream_t stream);
