@@ -11,5 +11,5 @@ timeout 300 $SHORT > gpurun_out/${TAG}_plain.log 2>&1 && \
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
     --log-file gpurun_out/${TAG}_launches.csv $SHORT > gpurun_out/${TAG}_ncu1.log 2>&1; echo "ncu list rc=$?"
 timeout 300 $SHORT > gpurun_out/${TAG}_plain2.log 2>&1 && \
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:corr_t -s 3 -c 2 \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:corr_ -s 3 -c 2 \
     -f -o gpurun_out/${TAG}_corr $SHORT > gpurun_out/${TAG}_ncu2.log 2>&1; echo "ncu full rc=$?"
