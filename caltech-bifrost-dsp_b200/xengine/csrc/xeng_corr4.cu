@@ -1,0 +1,358 @@
+// Corr, swizzled-raw plane-split TMA-fed variant: the production kernel (ninput % 16 == 0, 16-byte aligned buffers).
+//
+// Same contraction, tiling, operand planes and output order as xeng_corr3.cu.  What changed, and why (ncu source
+// view of corr_planes_kernel, profiles/r01c_*): the kernel was bound by instruction issue / the ALU pipe on the two
+// SM sub-partitions that also hosted the bulk-copy issuing warps, not by shared memory or the tensor pipe.
+//
+//   * raw boxes are fetched with SWIZZLE_128B, and an unpack thread owns 32 consecutive inputs of ONE sample
+//     (two LDS.128 of one row).  The B-column reorder n = b0*64 + a0*2 + p0 then needs 8 PRMT per thread and no
+//     SHFL / SEL / lane exchange; lanes run sample-fastest, so the operand STS.128 of a quarter-warp are 128
+//     contiguous bytes (no SBO skew) and the swizzle keeps the row-strided LDS.128 conflict-free.
+//   * bulk copies of the epilogue are issued by all four epilogue warps (16 runs each) from warp-uniform
+//     arithmetic, one elected lane, ~8 instructions per copy instead of the ~28 of ptxas' per-lane waterfall.
+//   * ablation switches compiled out of the production instantiation (they cost ~40 register moves per stage).
+//
+// Roles (448 threads): warps 0-3 epilogue, 4-7 unpack group 0, 8-11 unpack group 1, 12 TMA producer, 13 MMA issuer.
+#include <cuda.h>
+
+#include "xeng_ptx.cuh"
+#include "xeng_internal.h"
+
+namespace xeng {
+namespace {
+
+constexpr int TILE = 128;
+constexpr int PAIRS = TILE / 4;                            // stand pairs per tile side
+constexpr int ST_T = 32;                                   // samples per stage = K of one MMA
+constexpr int NSTAGE = 4;                                  // operand ring depth
+constexpr int RAW_STAGES = 8;                              // raw ring depth
+constexpr int RAW_PANEL = ST_T * TILE;                     // 4 KB: [32 samples][128 inputs], 128B-swizzled
+constexpr int RAW_STAGE_BYTES = 2 * RAW_PANEL;             // A | B
+constexpr int KGRP_BYTES = 128;                            // core matrix: 8 samples x 16 inputs
+constexpr int SBO = (ST_T / 8) * KGRP_BYTES;               // 512
+constexpr int PLANE = (TILE / 16) * SBO;                   // 4096
+constexpr int STAGE_BYTES = 5 * PLANE;                     // A_re | A_im | B_im | B_re | B_nim
+constexpr int OFF_A_RE = 0, OFF_A_IM = PLANE, OFF_B_IM = 2 * PLANE, OFF_B_RE = 3 * PLANE, OFF_B_NIM = 4 * PLANE;
+constexpr int RUN_BYTES = PAIRS * 16;                      // 32 cells x 4 words
+constexpr int RUN_STRIDE = RUN_BYTES + 16;
+constexpr int SLICE_RUNS = 2 * PAIRS;                      // 2 quadrants x 32 row pairs
+constexpr int HALF_SKEW = 64;                              // quadrant half b1 = 1 starts 64 B later (bank skew)
+constexpr int STAGING_BYTES = SLICE_RUNS * RUN_STRIDE + HALF_SKEW + 64;   // 33 920, multiple of 128
+constexpr int N_EPI_WARPS = 4, N_GROUP_WARPS = 4, N_GROUPS = 2;
+constexpr int RUNS_PER_WARP = SLICE_RUNS / N_EPI_WARPS;    // 16
+constexpr int WARP_TMA = N_EPI_WARPS + N_GROUPS * N_GROUP_WARPS, WARP_MMA = WARP_TMA + 1;
+constexpr int N_THREADS = (WARP_MMA + 1) * 32;
+constexpr int N_GROUP = N_GROUP_WARPS * 32;                // threads per unpack group
+constexpr int TMEM_COLS = 512;
+
+struct SmemHdr {
+  uint64_t raw_full[RAW_STAGES];
+  uint64_t raw_empty[RAW_STAGES];
+  uint64_t full[NSTAGE];
+  uint64_t empty[NSTAGE];
+  uint64_t tmem_full[2];
+  uint64_t tmem_empty[2];
+  uint32_t tmem_base;
+};
+constexpr int SMEM_HDR = 1024;                             // keeps the swizzled raw panels 1024-byte aligned
+static_assert(sizeof(SmemHdr) <= SMEM_HDR, "header");
+static_assert(STAGE_BYTES % 128 == 0 && STAGING_BYTES % 128 == 0, "alignment");
+constexpr int SMEM_BYTES = SMEM_HDR + RAW_STAGES * RAW_STAGE_BYTES + NSTAGE * STAGE_BYTES + 2 * STAGING_BYTES + 1024;
+static_assert(SMEM_BYTES <= 232448, "shared memory budget");
+
+constexpr uint32_t IDESC = umma_idesc(2, 1, 1, 1, 1, 128, 256);
+
+struct Tile {
+  int c, I, J;
+};
+__device__ __forceinline__ Tile decode_tile(int tile, int tiles_per_chan) {
+  Tile t;
+  t.c = tile / tiles_per_chan;
+  int r = tile - t.c * tiles_per_chan;
+  int I = static_cast<int>((sqrtf(8.f * r + 1.f) - 1.f) * 0.5f);
+  while ((I + 1) * (I + 2) / 2 <= r) ++I;
+  while (I * (I + 1) / 2 > r) --I;
+  t.I = I;
+  t.J = r - I * (I + 1) / 2;
+  return t;
+}
+
+__device__ __forceinline__ uint4 re16(uint4 x) {
+  return make_uint4(unpack_re4(x.x), unpack_re4(x.y), unpack_re4(x.z), unpack_re4(x.w));
+}
+__device__ __forceinline__ uint4 im16(uint4 x) {
+  return make_uint4(unpack_im4(x.x), unpack_im4(x.y), unpack_im4(x.z), unpack_im4(x.w));
+}
+__device__ __forceinline__ uint4 neg16(uint4 x) { return make_uint4(neg4(x.x), neg4(x.y), neg4(x.z), neg4(x.w)); }
+
+// 32 raw bytes of one sample = 8 stand pairs x (b0, p0).  Column unit of stand parity b0: the half-words b0 of the
+// eight words, i.e. 8 pairs x 2 pols = 16 columns n = a0*2 + p0.
+__device__ __forceinline__ uint4 parity_lo(uint4 a, uint4 b) {
+  return make_uint4(__byte_perm(a.x, a.y, 0x5410), __byte_perm(a.z, a.w, 0x5410), __byte_perm(b.x, b.y, 0x5410),
+                    __byte_perm(b.z, b.w, 0x5410));
+}
+__device__ __forceinline__ uint4 parity_hi(uint4 a, uint4 b) {
+  return make_uint4(__byte_perm(a.x, a.y, 0x7632), __byte_perm(a.z, a.w, 0x7632), __byte_perm(b.x, b.y, 0x7632),
+                    __byte_perm(b.z, b.w, 0x7632));
+}
+
+template <bool ABL>
+__global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_constant__ CUtensorMap tmap, CorrArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  SmemHdr* S = reinterpret_cast<SmemHdr*>(smem);
+  uint8_t* raw = smem + SMEM_HDR;
+  uint8_t* stages = raw + RAW_STAGES * RAW_STAGE_BYTES;
+  uint8_t* staging = stages + NSTAGE * STAGE_BYTES;
+
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);   // warp-uniform for ptxas
+  const int lane = threadIdx.x & 31;
+  const int n_kstage = (a.ntime + ST_T - 1) / ST_T;     // the TMA zero-fills samples past ntime
+  const int ablate = ABL ? a.ablate : 0;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < RAW_STAGES; ++s) {
+      mbar_init(&S->raw_full[s], 1);
+      mbar_init(&S->raw_empty[s], N_GROUP);
+    }
+    for (int s = 0; s < NSTAGE; ++s) {
+      mbar_init(&S->full[s], N_GROUP);
+      mbar_init(&S->empty[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&S->tmem_full[b], 1);
+      mbar_init(&S->tmem_empty[b], N_EPI_WARPS * 32);
+    }
+    mbar_fence_init();
+  }
+  if (warp == WARP_MMA) {
+    tmem_alloc(&S->tmem_base, TMEM_COLS);
+    tmem_relinquish();
+  }
+  if (warp == WARP_TMA && lane == 0) tma_prefetch_desc(&tmap);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = S->tmem_base;
+
+  if (warp < N_EPI_WARPS) {
+    // ===================================================================== epilogue
+    const int m = threadIdx.x;  // TMEM lane == tile row == in1 - 128*I = 4*A1loc + 2*b1 + p1
+    const int A1loc = m >> 2, b1 = (m >> 1) & 1, p1 = m & 1;
+    const long plane_words = static_cast<long>(a.nchan) * a.words_per_chan;
+    const uint32_t stg0 = smem_u32(staging);
+    const uint32_t my_run = stg0 + (b1 * PAIRS + A1loc) * RUN_STRIDE + b1 * HALF_SKEW + p1 * 8;
+    // bulk-copy issue role: lane 0 of warp w issues runs w*16 .. w*16+15 of every slice (run = rb1*32 + row pair)
+    const int rb1 = warp >> 1, k0 = (warp & 1) * RUNS_PER_WARP;
+    const uint32_t run_src0 = stg0 + (rb1 * PAIRS + k0) * RUN_STRIDE + rb1 * HALF_SKEW;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
+      const Tile tl = decode_tile(tile, a.tiles_per_chan);
+      const int buf = it & 1;
+      mbar_wait(&S->tmem_full[buf], (it >> 1) & 1, a.err, 100 + buf);
+      tc_fence_after();
+      const bool diag = (tl.I == tl.J);
+      const int A0base = tl.J * PAIRS;
+      const int rA1_0 = tl.I * PAIRS + k0;                              // first row pair this warp issues
+      const int ncell_max = min(PAIRS, a.npairs - A0base);
+      const long cell_0 = (static_cast<long>(rA1_0) * (rA1_0 + 1)) / 2 + A0base;
+      int32_t* const out_c = a.out + static_cast<long>(tl.c) * a.words_per_chan;
+#pragma unroll 1
+      for (int sl = 0; sl < 4; ++sl) {        // slice = (plane, b0): 64 accumulator columns
+        const int plane = sl >> 1, b0 = sl & 1;
+        const uint32_t stg_off = (sl & 1) * STAGING_BYTES;
+        // the copies issued two slices ago read this staging buffer: drain them, then sync the warps
+        bulk_wait_read<1>();   // groups live in the elected lane; empty elsewhere
+        named_bar_sync(1, N_EPI_WARPS * 32);
+        uint32_t r0[32], r1[32];
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(warp * 32) << 16) +
+                               static_cast<uint32_t>(buf * 256 + plane * 128 + b0 * 64);
+        tmem_ld_32x32b_x32(taddr, r0);
+        tmem_ld_32x32b_x32(taddr + 32, r1);
+        tmem_ld_wait();
+        if (sl == 3) {  // accumulator fully read: hand the TMEM buffer back to the MMA warp
+          tc_fence_before();
+          mbar_arrive(&S->tmem_empty[buf]);
+        }
+        if (!(ablate & 2)) {
+#pragma unroll
+          for (int a0 = 0; a0 < 16; ++a0) sts_v2(my_run + stg_off + a0 * 16, r0[2 * a0], r0[2 * a0 + 1]);
+#pragma unroll
+          for (int a0 = 0; a0 < 16; ++a0) sts_v2(my_run + stg_off + (a0 + 16) * 16, r1[2 * a0], r1[2 * a0 + 1]);
+          // unused xGPU padding cell of a diagonal tile (a0 == a1 in swapped order) is written as 0
+          if (diag && b0 == 1 && b1 == 0) sts_v2(my_run + stg_off + A1loc * 16, 0u, 0u);
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(1, N_EPI_WARPS * 32);
+        {   // warp-uniform: every lane walks the 16 runs, the elected lane issues
+          int32_t* dst = out_c + plane * plane_words + ((static_cast<long>(2 * b0 + rb1) * a.quad_cells + cell_0) << 2);
+          uint32_t src = run_src0 + stg_off;
+          int rA1 = rA1_0;
+          int nrow = min(RUNS_PER_WARP, a.npairs - rA1_0);     // row pairs of this warp that exist
+          if (ablate & 1) nrow = 0;
+          if (a.accumulate) {
+#pragma unroll
+            for (int k = 0; k < RUNS_PER_WARP; ++k) {
+              const int n = min(diag ? (k0 + k + 1) : PAIRS, ncell_max);
+              if (k < nrow) bulk_reduce_add_s32_elect(dst, src, n * 16);
+              ++rA1;
+              dst += rA1 << 2;         // next row pair of the triangle starts rA1+1 cells later
+              src += RUN_STRIDE;
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < RUNS_PER_WARP; ++k) {
+              const int n = min(diag ? (k0 + k + 1) : PAIRS, ncell_max);
+              if (k < nrow) bulk_store_elect(dst, src, n * 16);
+              ++rA1;
+              dst += rA1 << 2;
+              src += RUN_STRIDE;
+            }
+          }
+          bulk_commit();
+        }
+      }
+    }
+    bulk_wait<0>();
+  } else if (warp < WARP_TMA) {
+    // ===================================================================== unpack: raw ring -> operand planes
+    const int grp = (warp - N_EPI_WARPS) / N_GROUP_WARPS;          // stages with (index & 1) == grp
+    const int wg = (warp - N_EPI_WARPS) % N_GROUP_WARPS;
+    const int tlow = lane & 7, c = lane >> 3;                        // sample wg*8 + tlow, inputs 32c .. 32c+31
+    // swizzled raw row: logical 16-byte chunk j of row t sits at chunk j ^ (t & 7)
+    const uint32_t lds_a = (wg * 8 + tlow) * TILE + (((2 * c) ^ tlow) << 4), lds_b = lds_a ^ 16u;
+    const uint32_t kofs = wg * KGRP_BYTES + tlow * 16;               // K position inside a 16-input group
+    const uint32_t stsA = (2 * c) * SBO + kofs;                      // tile rows 32c .. 32c+15, next group +SBO
+    const uint32_t stsB = c * SBO + kofs;                            // columns n = 16c .. (b0 = 0), +4*SBO for b0 = 1
+    const uint32_t raw0 = smem_u32(raw), stages0 = smem_u32(stages);
+    int gs0 = 0;                                                     // running stage index at the tile start
+    for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, gs0 += n_kstage) {
+      const Tile tl = decode_tile(tile, a.tiles_per_chan);
+      const uint32_t boff = (tl.I == tl.J) ? 0u : static_cast<uint32_t>(RAW_PANEL);   // diagonal: B raw == A raw
+      for (int ks = (gs0 ^ grp) & 1; ks < n_kstage; ks += 2) {
+        const int gs = gs0 + ks;
+        const int rs = gs % RAW_STAGES, slot = gs % NSTAGE;
+        mbar_wait(&S->raw_full[rs], (gs / RAW_STAGES) & 1, a.err, 500 + rs);
+        const uint32_t rbase = raw0 + rs * RAW_STAGE_BYTES;
+        const uint4 rawA0 = lds_v4(rbase + lds_a), rawA1 = lds_v4(rbase + lds_b);
+        const uint4 rawB0 = lds_v4(rbase + boff + lds_a), rawB1 = lds_v4(rbase + boff + lds_b);
+        mbar_arrive(&S->raw_empty[rs]);     // raw bytes are in registers: the TMA warp may refill the slot
+        const uint4 colB0 = parity_lo(rawB0, rawB1), colB1 = parity_hi(rawB0, rawB1);
+        uint4 reA0, imA0, reA1, imA1, reB0, imB0, reB1, imB1, nimB0, nimB1;
+        if (ABL && (ablate & 16)) {
+          reA0 = imA0 = rawA0; reA1 = imA1 = rawA1; reB0 = imB0 = nimB0 = colB0; reB1 = imB1 = nimB1 = colB1;
+        } else {
+          reA0 = re16(rawA0); imA0 = im16(rawA0); reA1 = re16(rawA1); imA1 = im16(rawA1);
+          reB0 = re16(colB0); imB0 = im16(colB0); reB1 = re16(colB1); imB1 = im16(colB1);
+          nimB0 = neg16(imB0); nimB1 = neg16(imB1);
+        }
+        mbar_wait(&S->empty[slot], ((gs / NSTAGE) & 1) ^ 1, a.err, 200 + slot);
+        if (!(ablate & 8)) {
+          const uint32_t base = stages0 + slot * STAGE_BYTES;
+          sts_v4(base + OFF_A_RE + stsA, reA0);
+          sts_v4(base + OFF_A_RE + stsA + SBO, reA1);
+          sts_v4(base + OFF_A_IM + stsA, imA0);
+          sts_v4(base + OFF_A_IM + stsA + SBO, imA1);
+          sts_v4(base + OFF_B_IM + stsB, imB0);
+          sts_v4(base + OFF_B_IM + stsB + 4 * SBO, imB1);
+          sts_v4(base + OFF_B_RE + stsB, reB0);
+          sts_v4(base + OFF_B_RE + stsB + 4 * SBO, reB1);
+          sts_v4(base + OFF_B_NIM + stsB, nimB0);
+          sts_v4(base + OFF_B_NIM + stsB + 4 * SBO, nimB1);
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(&S->full[slot]);
+      }
+    }
+  } else if (warp == WARP_TMA) {
+    // ===================================================================== TMA producer (one lane)
+    if (lane == 0) {
+      int gs = 0;
+      for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
+        const Tile tl = decode_tile(tile, a.tiles_per_chan);
+        const bool diag = (tl.I == tl.J);
+        for (int ks = 0; ks < n_kstage; ++ks, ++gs) {
+          const int rs = gs % RAW_STAGES;
+          mbar_wait(&S->raw_empty[rs], ((gs / RAW_STAGES) & 1) ^ 1, a.err, 600 + rs);
+          const uint32_t dst = smem_u32(raw + rs * RAW_STAGE_BYTES);
+          if (ABL && (ablate & 32)) { mbar_arrive(&S->raw_full[rs]); continue; }
+          mbar_arrive_expect_tx(&S->raw_full[rs], diag ? RAW_PANEL : RAW_STAGE_BYTES);
+          tma_load_3d(dst, &tmap, &S->raw_full[rs], tl.I * TILE, tl.c, ks * ST_T);
+          if (!diag) tma_load_3d(dst + RAW_PANEL, &tmap, &S->raw_full[rs], tl.J * TILE, tl.c, ks * ST_T);
+        }
+      }
+    }
+  } else {
+    // ===================================================================== MMA issuer (one lane)
+    if (lane == 0) {
+      int gs = 0, it = 0;
+      for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
+        const int buf = it & 1;
+        mbar_wait(&S->tmem_empty[buf], ((it >> 1) & 1) ^ 1, a.err, 300 + buf);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + buf * 256;
+        for (int ks = 0; ks < n_kstage; ++ks, ++gs) {
+          const int slot = gs % NSTAGE;
+          mbar_wait(&S->full[slot], (gs / NSTAGE) & 1, a.err, 400 + slot);
+          tc_fence_after();
+          const uint32_t sbase = smem_u32(stages + slot * STAGE_BYTES);
+          if (!(ablate & 4)) {
+            // [ re1 re0 | -re1 im0 ] += A_re x [B_re | B_nim]^T ;  [ im1 im0 | im1 re0 ] += A_im x [B_im | B_re]^T
+            umma_i8_ss(tmem_d, umma_smem_desc(sbase + OFF_A_RE, KGRP_BYTES, SBO),
+                       umma_smem_desc(sbase + OFF_B_RE, KGRP_BYTES, SBO), IDESC, ks != 0);
+            umma_i8_ss(tmem_d, umma_smem_desc(sbase + OFF_A_IM, KGRP_BYTES, SBO),
+                       umma_smem_desc(sbase + OFF_B_IM, KGRP_BYTES, SBO), IDESC, 1);
+          }
+          umma_commit(&S->empty[slot]);
+          if (ks == n_kstage - 1) umma_commit(&S->tmem_full[buf]);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == WARP_MMA) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+}  // namespace
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+cudaError_t launch_corr_swz(const CorrArgs& a, int nsm, cudaStream_t stream) {
+  static EncodeTiledFn encode = nullptr;
+  static bool configured = false;
+  if (!configured) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess) return e;
+    if (qres != cudaDriverEntryPointSuccess || !fn) return cudaErrorNotSupported;
+    encode = reinterpret_cast<EncodeTiledFn>(fn);
+    e = cudaFuncSetAttribute(corr_swz_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(corr_swz_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  int grid = a.ntiles < nsm ? a.ntiles : nsm;
+  if (grid <= 0) return cudaSuccess;
+  alignas(64) CUtensorMap tmap;
+  const cuuint64_t gdim[3] = {static_cast<cuuint64_t>(a.ninput), static_cast<cuuint64_t>(a.nchan),
+                              static_cast<cuuint64_t>(a.ntime)};
+  const cuuint64_t gstride[2] = {static_cast<cuuint64_t>(a.ninput),
+                                 static_cast<cuuint64_t>(a.ninput) * static_cast<cuuint64_t>(a.nchan)};
+  const cuuint32_t box[3] = {TILE, 1, ST_T};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<uint8_t*>(a.in), gdim, gstride, box, estr,
+                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
+  if (a.ablate) corr_swz_kernel<true><<<grid, N_THREADS, SMEM_BYTES, stream>>>(tmap, a);
+  else corr_swz_kernel<false><<<grid, N_THREADS, SMEM_BYTES, stream>>>(tmap, a);
+  return cudaGetLastError();
+}
+
+}  // namespace xeng

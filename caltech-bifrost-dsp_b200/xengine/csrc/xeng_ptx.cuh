@@ -146,6 +146,25 @@ __device__ __forceinline__ void bulk_reduce_add_s32(void* gdst, uint32_t ssrc, u
                "r"(bytes)
                : "memory");
 }
+// Warp-collective variants: every lane executes the call with identical (warp-uniform) operands, one elected lane
+// issues.  Keeping the control flow convergent lets ptxas keep the operands in uniform registers instead of emitting
+// its per-lane R2UR waterfall loop.  elect.sync returns the same leader for the same member mask every time, so the
+// bulk groups stay with one thread; commit/wait executed by the other lanes act on empty groups.
+__device__ __forceinline__ void bulk_store_elect(void* gdst, uint32_t ssrc, uint32_t bytes) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "@p cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n\t}" ::"l"(gdst), "r"(ssrc), "r"(bytes)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_reduce_add_s32_elect(void* gdst, uint32_t ssrc, uint32_t bytes) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "@p cp.reduce.async.bulk.global.shared::cta.bulk_group.add.s32 [%0], [%1], %2;\n\t}" ::"l"(gdst), "r"(ssrc),
+      "r"(bytes)
+      : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void bulk_wait_read() {
