@@ -146,6 +146,15 @@ static int corr_launch(xeng_corr_t h, const void* d_in, int32_t* d_out, int accu
     const char* ab = getenv("XENG_CORR_ABLATE");   // developer-only timing ablations
     a.ablate = ab ? atoi(ab) : 0;
   }
+  a.trace = nullptr;
+  const char* trace_path = getenv("XENG_CORR_TRACE");   // developer-only: per-role clock64 timeline of CTA 0
+  static long long* d_trace = nullptr;
+  const size_t trace_bytes = 5 * 4096 * 2 * sizeof(long long);
+  if (trace_path && a.ablate) {
+    if (!d_trace) XENG_CUDA(cudaMalloc(reinterpret_cast<void**>(&d_trace), trace_bytes));
+    XENG_CUDA(cudaMemsetAsync(d_trace, 0, trace_bytes, h->stream));
+    a.trace = d_trace;
+  }
   a.words_per_chan = h->words_per_chan;
   a.quad_cells = h->quad_cells;
   if ((reinterpret_cast<uintptr_t>(d_out) & 15) != 0) return fail(XENG_ERR_ARG, "visibility buffer must be 16-byte aligned");
@@ -154,6 +163,16 @@ static int corr_launch(xeng_corr_t h, const void* d_in, int32_t* d_out, int accu
   else if (h->impl == 4 && xeng::corr_tma_supported(a)) XENG_CUDA(xeng::launch_corr_planes(a, h->nsm, h->stream));
   else if (h->impl == 3 && xeng::corr_tma_supported(a)) XENG_CUDA(xeng::launch_corr_tma(a, h->nsm, h->stream));
   else XENG_CUDA(xeng::launch_corr_tc(a, h->nsm, h->stream));   // register-fed tcgen05 kernel: any ninput / alignment
+  if (a.trace) {
+    XENG_CUDA(cudaStreamSynchronize(h->stream));
+    long long* host = static_cast<long long*>(malloc(trace_bytes));
+    if (host) {
+      XENG_CUDA(cudaMemcpy(host, d_trace, trace_bytes, cudaMemcpyDeviceToHost));
+      FILE* f = fopen(trace_path, "wb");
+      if (f) { fwrite(host, 1, trace_bytes, f); fclose(f); }
+      free(host);
+    }
+  }
   return XENG_OK;
 }
 

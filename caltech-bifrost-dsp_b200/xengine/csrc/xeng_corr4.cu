@@ -12,7 +12,7 @@
 //     arithmetic, one elected lane, ~8 instructions per copy instead of the ~28 of ptxas' per-lane waterfall.
 //   * ablation switches compiled out of the production instantiation (they cost ~40 register moves per stage).
 //
-// Roles (448 threads): warps 0-3 epilogue, 4-7 unpack group 0, 8-11 unpack group 1, 12 TMA producer, 13 MMA issuer.
+// Roles (576 threads): warps 0-7 epilogue, 8-11 unpack group 0, 12-15 unpack group 1, 16 TMA producer, 17 MMA issuer.
 #include <cuda.h>
 
 #include "xeng_ptx.cuh"
@@ -35,11 +35,9 @@ constexpr int STAGE_BYTES = 5 * PLANE;                     // A_re | A_im | B_im
 constexpr int OFF_A_RE = 0, OFF_A_IM = PLANE, OFF_B_IM = 2 * PLANE, OFF_B_RE = 3 * PLANE, OFF_B_NIM = 4 * PLANE;
 constexpr int RUN_BYTES = PAIRS * 16;                      // 32 cells x 4 words
 constexpr int RUN_STRIDE = RUN_BYTES + 16;
-constexpr int SLICE_RUNS = 2 * PAIRS;                      // 2 quadrants x 32 row pairs
 constexpr int HALF_SKEW = 64;                              // quadrant half b1 = 1 starts 64 B later (bank skew)
-constexpr int STAGING_BYTES = SLICE_RUNS * RUN_STRIDE + HALF_SKEW + 64;   // 33 920, multiple of 128
-constexpr int N_EPI_WARPS = 4, N_GROUP_WARPS = 4, N_GROUPS = 2;
-constexpr int RUNS_PER_WARP = SLICE_RUNS / N_EPI_WARPS;    // 16
+constexpr int WARP_STAGING = 16 * RUN_STRIDE + HALF_SKEW + 64;   // 8576: the 16 runs one epilogue warp stages
+constexpr int N_EPI_WARPS = 8, N_GROUP_WARPS = 4, N_GROUPS = 2;
 constexpr int WARP_TMA = N_EPI_WARPS + N_GROUPS * N_GROUP_WARPS, WARP_MMA = WARP_TMA + 1;
 constexpr int N_THREADS = (WARP_MMA + 1) * 32;
 constexpr int N_GROUP = N_GROUP_WARPS * 32;                // threads per unpack group
@@ -56,8 +54,8 @@ struct SmemHdr {
 };
 constexpr int SMEM_HDR = 1024;                             // keeps the swizzled raw panels 1024-byte aligned
 static_assert(sizeof(SmemHdr) <= SMEM_HDR, "header");
-static_assert(STAGE_BYTES % 128 == 0 && STAGING_BYTES % 128 == 0, "alignment");
-constexpr int SMEM_BYTES = SMEM_HDR + RAW_STAGES * RAW_STAGE_BYTES + NSTAGE * STAGE_BYTES + 2 * STAGING_BYTES + 1024;
+static_assert(STAGE_BYTES % 128 == 0 && WARP_STAGING % 128 == 0, "alignment");
+constexpr int SMEM_BYTES = SMEM_HDR + RAW_STAGES * RAW_STAGE_BYTES + NSTAGE * STAGE_BYTES + N_EPI_WARPS * WARP_STAGING + 1024;
 static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 
 constexpr uint32_t IDESC = umma_idesc(2, 1, 1, 1, 1, 128, 256);
@@ -96,6 +94,16 @@ __device__ __forceinline__ uint4 parity_hi(uint4 a, uint4 b) {
                     __byte_perm(b.z, b.w, 0x7632));
 }
 
+// developer timeline: role r appends (tag, clock64) pairs for CTA 0 (ablation instantiation only)
+#define XTRACE(role, tag)                                                                  \
+  do {                                                                                     \
+    if (ABL && a.trace && blockIdx.x == 0 && tcnt < 4096) {                                \
+      a.trace[((role) * 4096 + tcnt) * 2] = (tag);                                         \
+      a.trace[((role) * 4096 + tcnt) * 2 + 1] = clock64();                                 \
+      ++tcnt;                                                                              \
+    }                                                                                      \
+  } while (0)
+
 template <bool ABL>
 __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_constant__ CUtensorMap tmap, CorrArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -109,6 +117,8 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
   const int lane = threadIdx.x & 31;
   const int n_kstage = (a.ntime + ST_T - 1) / ST_T;     // the TMA zero-fills samples past ntime
   const int ablate = ABL ? a.ablate : 0;
+  int tcnt = 0;
+  (void)tcnt;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < RAW_STAGES; ++s) {
@@ -136,81 +146,83 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
   const uint32_t tmem_base = S->tmem_base;
 
   if (warp < N_EPI_WARPS) {
-    // ===================================================================== epilogue
-    const int m = threadIdx.x;  // TMEM lane == tile row == in1 - 128*I = 4*A1loc + 2*b1 + p1
-    const int A1loc = m >> 2, b1 = (m >> 1) & 1, p1 = m & 1;
+    // ===================================================================== epilogue (8 independent warps)
+    // Warp w reads TMEM lanes 32*(w & 3) .. +31 (tile rows m = 4*A1loc + 2*b1 + p1) and the accumulator columns of
+    // stand parity b0 = w >> 2, plane 0 then plane 1.  A lane stages only its own row, so the 16 runs a warp
+    // writes ((b1, 8 row pairs) x 32 cells x 16 B) are private to it: no cross-warp barrier, the warp issues the
+    // bulk copies of exactly the runs it staged and waits only for its own copies before reusing its buffer.
+    const int q = warp & 3, b0 = warp >> 2;
+    const int m = q * 32 + lane;
+    const int A1l = lane >> 2, b1 = (lane >> 1) & 1, p1 = lane & 1;   // A1loc = 8*q + A1l
     const long plane_words = static_cast<long>(a.nchan) * a.words_per_chan;
-    const uint32_t stg0 = smem_u32(staging);
-    const uint32_t my_run = stg0 + (b1 * PAIRS + A1loc) * RUN_STRIDE + b1 * HALF_SKEW + p1 * 8;
-    // bulk-copy issue role: lane 0 of warp w issues runs w*16 .. w*16+15 of every slice (run = rb1*32 + row pair)
-    const int rb1 = warp >> 1, k0 = (warp & 1) * RUNS_PER_WARP;
-    const uint32_t run_src0 = stg0 + (rb1 * PAIRS + k0) * RUN_STRIDE + rb1 * HALF_SKEW;
+    const uint32_t stg_w = smem_u32(staging) + warp * WARP_STAGING;
+    const uint32_t my_run = stg_w + (b1 * 8 + A1l) * RUN_STRIDE + b1 * HALF_SKEW + p1 * 8;
     int it = 0;
     for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
       const Tile tl = decode_tile(tile, a.tiles_per_chan);
       const int buf = it & 1;
+      if (warp == 0 && lane == 0) XTRACE(4, 10);
       mbar_wait(&S->tmem_full[buf], (it >> 1) & 1, a.err, 100 + buf);
+      if (warp == 0 && lane == 0) XTRACE(4, 11);
       tc_fence_after();
       const bool diag = (tl.I == tl.J);
       const int A0base = tl.J * PAIRS;
-      const int rA1_0 = tl.I * PAIRS + k0;                              // first row pair this warp issues
+      const int rA1_0 = tl.I * PAIRS + 8 * q;                            // first row pair of this warp
       const int ncell_max = min(PAIRS, a.npairs - A0base);
       const long cell_0 = (static_cast<long>(rA1_0) * (rA1_0 + 1)) / 2 + A0base;
+      int nrow = min(8, a.npairs - rA1_0);                               // row pairs of this warp that exist
+      if (ablate & 1) nrow = 0;
       int32_t* const out_c = a.out + static_cast<long>(tl.c) * a.words_per_chan;
 #pragma unroll 1
-      for (int sl = 0; sl < 4; ++sl) {        // slice = (plane, b0): 64 accumulator columns
-        const int plane = sl >> 1, b0 = sl & 1;
-        const uint32_t stg_off = (sl & 1) * STAGING_BYTES;
-        // the copies issued two slices ago read this staging buffer: drain them, then sync the warps
-        bulk_wait_read<1>();   // groups live in the elected lane; empty elsewhere
-        named_bar_sync(1, N_EPI_WARPS * 32);
-        uint32_t r0[32], r1[32];
-        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(warp * 32) << 16) +
+      for (int plane = 0; plane < 2; ++plane) {
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
                                static_cast<uint32_t>(buf * 256 + plane * 128 + b0 * 64);
+        uint32_t r0[32];
         tmem_ld_32x32b_x32(taddr, r0);
-        tmem_ld_32x32b_x32(taddr + 32, r1);
+        bulk_wait_read<0>();     // this warp's previous copies have left its staging buffer (groups: elected lane)
+        __syncwarp();
         tmem_ld_wait();
-        if (sl == 3) {  // accumulator fully read: hand the TMEM buffer back to the MMA warp
+        if (warp == 0 && lane == 0) XTRACE(4, 14);
+        if (!(ablate & 2)) {
+#pragma unroll
+          for (int a0 = 0; a0 < 16; ++a0) sts_v2(my_run + a0 * 16, r0[2 * a0], r0[2 * a0 + 1]);
+        }
+        tmem_ld_32x32b_x32(taddr + 32, r0);
+        tmem_ld_wait();
+        if (plane == 1) {  // accumulator fully read by this warp: hand the TMEM buffer back to the MMA warp
           tc_fence_before();
           mbar_arrive(&S->tmem_empty[buf]);
         }
         if (!(ablate & 2)) {
 #pragma unroll
-          for (int a0 = 0; a0 < 16; ++a0) sts_v2(my_run + stg_off + a0 * 16, r0[2 * a0], r0[2 * a0 + 1]);
-#pragma unroll
-          for (int a0 = 0; a0 < 16; ++a0) sts_v2(my_run + stg_off + (a0 + 16) * 16, r1[2 * a0], r1[2 * a0 + 1]);
+          for (int a0 = 0; a0 < 16; ++a0) sts_v2(my_run + (a0 + 16) * 16, r0[2 * a0], r0[2 * a0 + 1]);
           // unused xGPU padding cell of a diagonal tile (a0 == a1 in swapped order) is written as 0
-          if (diag && b0 == 1 && b1 == 0) sts_v2(my_run + stg_off + A1loc * 16, 0u, 0u);
+          if (diag && b0 == 1 && b1 == 0) sts_v2(my_run + (8 * q + A1l) * 16, 0u, 0u);
         }
+        if (warp == 0 && lane == 0) XTRACE(4, 15);
         fence_proxy_async_smem();
-        named_bar_sync(1, N_EPI_WARPS * 32);
-        {   // warp-uniform: every lane walks the 16 runs, the elected lane issues
+        __syncwarp();
+        if (warp == 0 && lane == 0) XTRACE(4, 16);
+        // warp-uniform: every lane walks the 16 runs (b1 = 0: 8 row pairs, b1 = 1: 8 row pairs), the elected lane issues
+#pragma unroll
+        for (int rb1 = 0; rb1 < 2; ++rb1) {
           int32_t* dst = out_c + plane * plane_words + ((static_cast<long>(2 * b0 + rb1) * a.quad_cells + cell_0) << 2);
-          uint32_t src = run_src0 + stg_off;
+          uint32_t src = stg_w + rb1 * (8 * RUN_STRIDE + HALF_SKEW);
           int rA1 = rA1_0;
-          int nrow = min(RUNS_PER_WARP, a.npairs - rA1_0);     // row pairs of this warp that exist
-          if (ablate & 1) nrow = 0;
-          if (a.accumulate) {
 #pragma unroll
-            for (int k = 0; k < RUNS_PER_WARP; ++k) {
-              const int n = min(diag ? (k0 + k + 1) : PAIRS, ncell_max);
-              if (k < nrow) bulk_reduce_add_s32_elect(dst, src, n * 16);
-              ++rA1;
-              dst += rA1 << 2;         // next row pair of the triangle starts rA1+1 cells later
-              src += RUN_STRIDE;
+          for (int k = 0; k < 8; ++k) {
+            const int n = min(diag ? (8 * q + k + 1) : PAIRS, ncell_max);
+            if (k < nrow) {
+              if (a.accumulate) bulk_reduce_add_s32_elect(dst, src, n * 16);
+              else bulk_store_elect(dst, src, n * 16);
             }
-          } else {
-#pragma unroll
-            for (int k = 0; k < RUNS_PER_WARP; ++k) {
-              const int n = min(diag ? (k0 + k + 1) : PAIRS, ncell_max);
-              if (k < nrow) bulk_store_elect(dst, src, n * 16);
-              ++rA1;
-              dst += rA1 << 2;
-              src += RUN_STRIDE;
-            }
+            ++rA1;
+            dst += rA1 << 2;           // next row pair of the triangle starts rA1+1 cells later
+            src += RUN_STRIDE;
           }
-          bulk_commit();
         }
+        bulk_commit();
+        if (warp == 0 && lane == 0) XTRACE(4, 17);
       }
     }
     bulk_wait<0>();
@@ -232,7 +244,9 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
       for (int ks = (gs0 ^ grp) & 1; ks < n_kstage; ks += 2) {
         const int gs = gs0 + ks;
         const int rs = gs % RAW_STAGES, slot = gs % NSTAGE;
+        if (wg == 0 && lane == 0) XTRACE(grp, 20);
         mbar_wait(&S->raw_full[rs], (gs / RAW_STAGES) & 1, a.err, 500 + rs);
+        if (wg == 0 && lane == 0) XTRACE(grp, 21);
         const uint32_t rbase = raw0 + rs * RAW_STAGE_BYTES;
         const uint4 rawA0 = lds_v4(rbase + lds_a), rawA1 = lds_v4(rbase + lds_b);
         const uint4 rawB0 = lds_v4(rbase + boff + lds_a), rawB1 = lds_v4(rbase + boff + lds_b);
@@ -246,7 +260,9 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
           reB0 = re16(colB0); imB0 = im16(colB0); reB1 = re16(colB1); imB1 = im16(colB1);
           nimB0 = neg16(imB0); nimB1 = neg16(imB1);
         }
+        if (wg == 0 && lane == 0) XTRACE(grp, 22);
         mbar_wait(&S->empty[slot], ((gs / NSTAGE) & 1) ^ 1, a.err, 200 + slot);
+        if (wg == 0 && lane == 0) XTRACE(grp, 23);
         if (!(ablate & 8)) {
           const uint32_t base = stages0 + slot * STAGE_BYTES;
           sts_v4(base + OFF_A_RE + stsA, reA0);
@@ -260,7 +276,9 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
           sts_v4(base + OFF_B_NIM + stsB, nimB0);
           sts_v4(base + OFF_B_NIM + stsB + 4 * SBO, nimB1);
         }
+        if (wg == 0 && lane == 0) XTRACE(grp, 24);
         fence_proxy_async_smem();
+        if (wg == 0 && lane == 0) XTRACE(grp, 25);
         mbar_arrive(&S->full[slot]);
       }
     }
@@ -273,7 +291,9 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
         const bool diag = (tl.I == tl.J);
         for (int ks = 0; ks < n_kstage; ++ks, ++gs) {
           const int rs = gs % RAW_STAGES;
+          XTRACE(3, 30);
           mbar_wait(&S->raw_empty[rs], ((gs / RAW_STAGES) & 1) ^ 1, a.err, 600 + rs);
+          XTRACE(3, 31);
           const uint32_t dst = smem_u32(raw + rs * RAW_STAGE_BYTES);
           if (ABL && (ablate & 32)) { mbar_arrive(&S->raw_full[rs]); continue; }
           mbar_arrive_expect_tx(&S->raw_full[rs], diag ? RAW_PANEL : RAW_STAGE_BYTES);
@@ -288,12 +308,16 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
       int gs = 0, it = 0;
       for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
         const int buf = it & 1;
+        XTRACE(2, 40);
         mbar_wait(&S->tmem_empty[buf], ((it >> 1) & 1) ^ 1, a.err, 300 + buf);
+        XTRACE(2, 41);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + buf * 256;
         for (int ks = 0; ks < n_kstage; ++ks, ++gs) {
           const int slot = gs % NSTAGE;
+          XTRACE(2, 42);
           mbar_wait(&S->full[slot], (gs / NSTAGE) & 1, a.err, 400 + slot);
+          XTRACE(2, 43);
           tc_fence_after();
           const uint32_t sbase = smem_u32(stages + slot * STAGE_BYTES);
           if (!(ablate & 4)) {
@@ -304,6 +328,7 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
                        umma_smem_desc(sbase + OFF_B_IM, KGRP_BYTES, SBO), IDESC, 1);
           }
           umma_commit(&S->empty[slot]);
+          XTRACE(2, 44);
           if (ks == n_kstage - 1) umma_commit(&S->tmem_full[buf]);
         }
       }

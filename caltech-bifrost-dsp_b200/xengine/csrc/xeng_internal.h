@@ -14,6 +14,7 @@ struct CorrArgs {
   int tiles_per_chan, ntiles;
   int accumulate;       // 0: out = X, 1: out += X
   int ablate;           // profiling ablation mask (XENG_CORR_ABLATE, results invalid when != 0)
+  long long* trace;     // developer timeline buffer (XENG_CORR_TRACE), null in production
   long words_per_chan;  // (nstand/2+1)*(nstand/4)*16
   long quad_cells;      // (nstand/2+1)*(nstand/4): cells per xGPU quadrant
 };
