@@ -342,7 +342,7 @@ def run_b200(args):
                     "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": d2h_total / K,
                     "ms_per_step": e2e_ms / K, "checksum": checksum},
             "gpu_launches": K,
-            "roofline": {"kernel": "corr_planes_kernel (fused Corr+CorrAcc)", "bound": "hbm", "achieved": achieved,
+            "roofline": {"kernel": "corr_swz_kernel (fused Corr+CorrAcc)", "bound": "hbm", "achieved": achieved,
                          "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
                          "peak_source": peak_src, "alg_bytes_per_launch": alg_bytes, "kernel_ms": kern_ms,
                          "tensor": {"useful_int8_tops": useful_tops, "nominal_peak_tops": INT8_NOMINAL_TOPS,

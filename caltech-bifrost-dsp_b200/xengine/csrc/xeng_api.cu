@@ -124,8 +124,8 @@ int xeng_corr_set_stream(xeng_corr_t h, void* s) {
 }
 int xeng_corr_set_impl(xeng_corr_t h, int impl) {
   if (!h) return fail(XENG_ERR_ARG, "null handle");
-  if (impl < 0 || impl > 4)
-    return fail(XENG_ERR_ARG, "impl must be 0 (tcgen05, auto), 1 (CUDA-core cross-check), 2 (register-fed tcgen05), 3 (interleaved-panel TMA tcgen05) or 4 (plane-split TMA tcgen05)");
+  if (impl < 0 || impl > 2)
+    return fail(XENG_ERR_ARG, "impl must be 0 (tcgen05, auto: TMA-fed when the shape allows), 1 (CUDA-core cross-check) or 2 (register-fed tcgen05)");
   h->impl = impl;
   return XENG_OK;
 }
@@ -160,8 +160,6 @@ static int corr_launch(xeng_corr_t h, const void* d_in, int32_t* d_out, int accu
   if ((reinterpret_cast<uintptr_t>(d_out) & 15) != 0) return fail(XENG_ERR_ARG, "visibility buffer must be 16-byte aligned");
   if (h->impl == 1) XENG_CUDA(xeng::launch_corr_simt(a, h->stream));
   else if (h->impl == 0 && xeng::corr_tma_supported(a)) XENG_CUDA(xeng::launch_corr_swz(a, h->nsm, h->stream));
-  else if (h->impl == 4 && xeng::corr_tma_supported(a)) XENG_CUDA(xeng::launch_corr_planes(a, h->nsm, h->stream));
-  else if (h->impl == 3 && xeng::corr_tma_supported(a)) XENG_CUDA(xeng::launch_corr_tma(a, h->nsm, h->stream));
   else XENG_CUDA(xeng::launch_corr_tc(a, h->nsm, h->stream));   // register-fed tcgen05 kernel: any ninput / alignment
   if (a.trace) {
     XENG_CUDA(cudaStreamSynchronize(h->stream));

@@ -1,16 +1,33 @@
-// Corr, swizzled-raw plane-split TMA-fed variant: the production kernel (ninput % 16 == 0, 16-byte aligned buffers).
+// Corr (+ fused CorrAcc): the production kernel, TMA-fed tcgen05 (ninput % 16 == 0, 16-byte aligned buffers).
 //
-// Same contraction, tiling, operand planes and output order as xeng_corr3.cu.  What changed, and why (ncu source
-// view of corr_planes_kernel, profiles/r01c_*): the kernel was bound by instruction issue / the ALU pipe on the two
-// SM sub-partitions that also hosted the bulk-copy issuing warps, not by shared memory or the tensor pipe.
+// Contraction (corr_block.py:445 / xgpu_test.py:102-136): per channel, word regtile_index(in0, in1) = sum_t conj(v[in0]) v[in1]
+// for every station pair a1 >= a0, written in xGPU's register-tile order.  Here: a K-stacked int8 GEMM on the 5th-gen
+// tensor cores with int32 accumulators in TMEM.
 //
-//   * raw boxes are fetched with SWIZZLE_128B, and an unpack thread owns 32 consecutive inputs of ONE sample
-//     (two LDS.128 of one row).  The B-column reorder n = b0*64 + a0*2 + p0 then needs 8 PRMT per thread and no
-//     SHFL / SEL / lane exchange; lanes run sample-fastest, so the operand STS.128 of a quarter-warp are 128
-//     contiguous bytes (no SBO skew) and the swizzle keeps the row-strided LDS.128 conflict-free.
-//   * bulk copies of the epilogue are issued by all four epilogue warps (16 runs each) from warp-uniform
-//     arithmetic, one elected lane, ~8 instructions per copy instead of the ~28 of ptxas' per-lane waterfall.
-//   * ablation switches compiled out of the production instantiation (they cost ~40 register moves per stage).
+//   tile      (channel, 128 "row" inputs I, 128 "column" inputs J <= I); persistent grid, one CTA per SM, static
+//             round-robin over tiles; TMEM holds two 256-column accumulators [Re(128) | Im(128)] (double buffered).
+//   TMA warp  cp.async.bulk.tensor.3d boxes {128 inputs, 1 channel, 64 samples} of RAW 4+4-bit bytes, SWIZZLE_128B,
+//             into a 4-deep ring (diagonal tiles fetch one panel).
+//   unpack    2 groups x 4 warps on alternate stages.  A thread owns 32 consecutive inputs of one sample per
+//             32-sample K-block (two LDS.128 of one swizzled row: conflict-free), sign-extends nibbles with SWAR
+//             arithmetic and writes five int8 operand planes in tcgen05's MN-major no-swizzle core-matrix layout:
+//             A_re, A_im (rows) and B_im, B_re, B_nim = -B_im (columns, reordered n = b0*64 + a0*2 + p0 with 8 PRMT).
+//             Planes are contiguous along MN, so an N = 256 operand runs from one plane into the next:
+//                 D[128 x 256] += A_re x [B_re | B_nim]^T      ->  [ re1 re0 | -re1 im0 ]
+//                 D[128 x 256] += A_im x [B_im | B_re ]^T      ->  [ im1 im0 |  im1 re0 ]
+//             Lanes run sample-fastest: the STS.128 of a quarter-warp are 128 contiguous bytes (conflict-free).
+//             The raw slot is handed back with an arrive that is ordered after the LDS *data* (mbar_arrive_after).
+//   MMA warp  one lane issues tcgen05.mma.kind::i8 M=128 N=256 K=32 (4 per stage), tcgen05.commit -> mbarriers.
+//   epilogue  8 independent warps.  Warp w reads TMEM lanes 32*(w&3).. and the columns of stand parity b0 = w>>2
+//             (tcgen05.ld.32x32b.x32), stages its own 16 runs (run = 32 cells x 16 B, contiguous in xGPU order) in a
+//             private 8.4 KB buffer and issues their bulk copies itself: cp.async.bulk (store) or
+//             cp.reduce.async.bulk.add.s32 (fused CorrAcc: the read-modify-write happens in L2).  No cross-warp
+//             barrier; operands are warp-uniform so one elected lane issues without ptxas' per-lane waterfall.
+//
+// Why this shape (measurements: profiles/r01c_*, scripts/trace.py, scripts/ubench/bulk_rate.cu): a warp can issue one
+// bulk copy per ~80 cycles, so the 220 copies of a tile need >= 4 warps issuing concurrently; one MMA-issuing thread
+// needs >= 4 MMAs per barrier round trip to keep the tensor pipe fed; the bulk-reduce path itself sustains
+// 3.17 TB/s of payload (= HBM read + write), i.e. the HBM roofline.
 //
 // Roles (576 threads): warps 0-7 epilogue, 8-11 unpack group 0, 12-15 unpack group 1, 16 TMA producer, 17 MMA issuer.
 #include <cuda.h>
@@ -23,14 +40,15 @@ namespace {
 
 constexpr int TILE = 128;
 constexpr int PAIRS = TILE / 4;                            // stand pairs per tile side
-constexpr int ST_T = 32;                                   // samples per stage = K of one MMA
-constexpr int NSTAGE = 4;                                  // operand ring depth
-constexpr int RAW_STAGES = 8;                              // raw ring depth
-constexpr int RAW_PANEL = ST_T * TILE;                     // 4 KB: [32 samples][128 inputs], 128B-swizzled
+constexpr int ST_T = 64;                                   // samples per stage
+constexpr int KB = ST_T / 32;                              // MMA K-blocks (32 samples) per stage
+constexpr int NSTAGE = 2;                                  // operand ring depth
+constexpr int RAW_STAGES = 4;                              // raw ring depth
+constexpr int RAW_PANEL = ST_T * TILE;                     // 8 KB: [64 samples][128 inputs], 128B-swizzled
 constexpr int RAW_STAGE_BYTES = 2 * RAW_PANEL;             // A | B
 constexpr int KGRP_BYTES = 128;                            // core matrix: 8 samples x 16 inputs
-constexpr int SBO = (ST_T / 8) * KGRP_BYTES;               // 512
-constexpr int PLANE = (TILE / 16) * SBO;                   // 4096
+constexpr int SBO = (ST_T / 8) * KGRP_BYTES;               // 1024
+constexpr int PLANE = (TILE / 16) * SBO;                   // 8192
 constexpr int STAGE_BYTES = 5 * PLANE;                     // A_re | A_im | B_im | B_re | B_nim
 constexpr int OFF_A_RE = 0, OFF_A_IM = PLANE, OFF_B_IM = 2 * PLANE, OFF_B_RE = 3 * PLANE, OFF_B_NIM = 4 * PLANE;
 constexpr int RUN_BYTES = PAIRS * 16;                      // 32 cells x 4 words
@@ -52,7 +70,8 @@ struct SmemHdr {
   uint64_t tmem_empty[2];
   uint32_t tmem_base;
 };
-constexpr int SMEM_HDR = 1024;                             // keeps the swizzled raw panels 1024-byte aligned
+constexpr int SMEM_HDR = 2048;                             // barriers + 1 KB scratch; raw panels stay 1024-byte aligned
+constexpr int SCRATCH_OFF = 1024;                          // one dummy word per unpack thread (mbar_arrive_after)
 static_assert(sizeof(SmemHdr) <= SMEM_HDR, "header");
 static_assert(STAGE_BYTES % 128 == 0 && WARP_STAGING % 128 == 0, "alignment");
 constexpr int SMEM_BYTES = SMEM_HDR + RAW_STAGES * RAW_STAGE_BYTES + NSTAGE * STAGE_BYTES + N_EPI_WARPS * WARP_STAGING + 1024;
@@ -94,14 +113,20 @@ __device__ __forceinline__ uint4 parity_hi(uint4 a, uint4 b) {
                     __byte_perm(b.z, b.w, 0x7632));
 }
 
-// developer timeline: role r appends (tag, clock64) pairs for CTA 0 (ablation instantiation only)
-#define XTRACE(role, tag)                                                                  \
+// developer phase timer: time since the previous mark is charged to bucket i of the calling thread; the buckets of
+// one thread per role of CTA 0 are written to a.trace at the end (ablation instantiation only, registers only)
+#define XTRACE(role, i)                                                                    \
   do {                                                                                     \
-    if (ABL && a.trace && blockIdx.x == 0 && tcnt < 4096) {                                \
-      a.trace[((role) * 4096 + tcnt) * 2] = (tag);                                         \
-      a.trace[((role) * 4096 + tcnt) * 2 + 1] = clock64();                                 \
-      ++tcnt;                                                                              \
+    if (ABL && a.trace) {                                                                  \
+      const uint32_t now__ = static_cast<uint32_t>(clock64());                             \
+      tacc[(i) & 7] += now__ - tlast;                                                      \
+      tlast = now__;                                                                       \
     }                                                                                      \
+  } while (0)
+#define XTRACE_DUMP(role)                                                                  \
+  do {                                                                                     \
+    if (ABL && a.trace && blockIdx.x == 0)                                                 \
+      for (int i__ = 0; i__ < 8; ++i__) a.trace[(role) * 8 + i__] = tacc[i__];             \
   } while (0)
 
 template <bool ABL>
@@ -117,8 +142,9 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
   const int lane = threadIdx.x & 31;
   const int n_kstage = (a.ntime + ST_T - 1) / ST_T;     // the TMA zero-fills samples past ntime
   const int ablate = ABL ? a.ablate : 0;
-  int tcnt = 0;
-  (void)tcnt;
+  uint32_t tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  uint32_t tlast = static_cast<uint32_t>(clock64());
+  (void)tacc; (void)tlast;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < RAW_STAGES; ++s) {
@@ -161,9 +187,9 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
     for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
       const Tile tl = decode_tile(tile, a.tiles_per_chan);
       const int buf = it & 1;
-      if (warp == 0 && lane == 0) XTRACE(4, 10);
+      XTRACE(4, 0);
       mbar_wait(&S->tmem_full[buf], (it >> 1) & 1, a.err, 100 + buf);
-      if (warp == 0 && lane == 0) XTRACE(4, 11);
+      XTRACE(4, 1);
       tc_fence_after();
       const bool diag = (tl.I == tl.J);
       const int A0base = tl.J * PAIRS;
@@ -182,7 +208,7 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
         bulk_wait_read<0>();     // this warp's previous copies have left its staging buffer (groups: elected lane)
         __syncwarp();
         tmem_ld_wait();
-        if (warp == 0 && lane == 0) XTRACE(4, 14);
+        XTRACE(4, 4);
         if (!(ablate & 2)) {
 #pragma unroll
           for (int a0 = 0; a0 < 16; ++a0) sts_v2(my_run + a0 * 16, r0[2 * a0], r0[2 * a0 + 1]);
@@ -199,10 +225,10 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
           // unused xGPU padding cell of a diagonal tile (a0 == a1 in swapped order) is written as 0
           if (diag && b0 == 1 && b1 == 0) sts_v2(my_run + (8 * q + A1l) * 16, 0u, 0u);
         }
-        if (warp == 0 && lane == 0) XTRACE(4, 15);
+        XTRACE(4, 5);
         fence_proxy_async_smem();
         __syncwarp();
-        if (warp == 0 && lane == 0) XTRACE(4, 16);
+        XTRACE(4, 6);
         // warp-uniform: every lane walks the 16 runs (b1 = 0: 8 row pairs, b1 = 1: 8 row pairs), the elected lane issues
 #pragma unroll
         for (int rb1 = 0; rb1 < 2; ++rb1) {
@@ -222,10 +248,11 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
           }
         }
         bulk_commit();
-        if (warp == 0 && lane == 0) XTRACE(4, 17);
+        XTRACE(4, 7);
       }
     }
     bulk_wait<0>();
+    if (warp == 0 && lane == 0) XTRACE_DUMP(4);
   } else if (warp < WARP_TMA) {
     // ===================================================================== unpack: raw ring -> operand planes
     const int grp = (warp - N_EPI_WARPS) / N_GROUP_WARPS;          // stages with (index & 1) == grp
@@ -237,6 +264,7 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
     const uint32_t stsA = (2 * c) * SBO + kofs;                      // tile rows 32c .. 32c+15, next group +SBO
     const uint32_t stsB = c * SBO + kofs;                            // columns n = 16c .. (b0 = 0), +4*SBO for b0 = 1
     const uint32_t raw0 = smem_u32(raw), stages0 = smem_u32(stages);
+    const uint32_t scratch = smem_u32(smem) + SCRATCH_OFF + (threadIdx.x - N_EPI_WARPS * 32) * 4;
     int gs0 = 0;                                                     // running stage index at the tile start
     for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, gs0 += n_kstage) {
       const Tile tl = decode_tile(tile, a.tiles_per_chan);
@@ -244,44 +272,71 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
       for (int ks = (gs0 ^ grp) & 1; ks < n_kstage; ks += 2) {
         const int gs = gs0 + ks;
         const int rs = gs % RAW_STAGES, slot = gs % NSTAGE;
-        if (wg == 0 && lane == 0) XTRACE(grp, 20);
+        XTRACE(grp, 0);
         mbar_wait(&S->raw_full[rs], (gs / RAW_STAGES) & 1, a.err, 500 + rs);
-        if (wg == 0 && lane == 0) XTRACE(grp, 21);
+        XTRACE(grp, 1);
         const uint32_t rbase = raw0 + rs * RAW_STAGE_BYTES;
-        const uint4 rawA0 = lds_v4(rbase + lds_a), rawA1 = lds_v4(rbase + lds_b);
-        const uint4 rawB0 = lds_v4(rbase + boff + lds_a), rawB1 = lds_v4(rbase + boff + lds_b);
-        mbar_arrive(&S->raw_empty[rs]);     // raw bytes are in registers: the TMA warp may refill the slot
-        const uint4 colB0 = parity_lo(rawB0, rawB1), colB1 = parity_hi(rawB0, rawB1);
-        uint4 reA0, imA0, reA1, imA1, reB0, imB0, reB1, imB1, nimB0, nimB1;
-        if (ABL && (ablate & 16)) {
-          reA0 = imA0 = rawA0; reA1 = imA1 = rawA1; reB0 = imB0 = nimB0 = colB0; reB1 = imB1 = nimB1 = colB1;
-        } else {
-          reA0 = re16(rawA0); imA0 = im16(rawA0); reA1 = re16(rawA1); imA1 = im16(rawA1);
-          reB0 = re16(colB0); imB0 = im16(colB0); reB1 = re16(colB1); imB1 = im16(colB1);
-          nimB0 = neg16(imB0); nimB1 = neg16(imB1);
+        const int nkb = min(KB, (a.ntime - ks * ST_T + 31) >> 5);      // K-blocks of this stage that hold samples
+        uint4 rawA[KB][2], rawB[KB][2];
+#pragma unroll
+        for (int j = 0; j < KB; ++j) {
+          if (j < nkb) {
+            rawA[j][0] = lds_v4(rbase + j * (32 * TILE) + lds_a);
+            rawA[j][1] = lds_v4(rbase + j * (32 * TILE) + lds_b);
+            rawB[j][0] = lds_v4(rbase + boff + j * (32 * TILE) + lds_a);
+            rawB[j][1] = lds_v4(rbase + boff + j * (32 * TILE) + lds_b);
+          }
         }
-        if (wg == 0 && lane == 0) XTRACE(grp, 22);
-        mbar_wait(&S->empty[slot], ((gs / NSTAGE) & 1) ^ 1, a.err, 200 + slot);
-        if (wg == 0 && lane == 0) XTRACE(grp, 23);
-        if (!(ablate & 8)) {
-          const uint32_t base = stages0 + slot * STAGE_BYTES;
-          sts_v4(base + OFF_A_RE + stsA, reA0);
-          sts_v4(base + OFF_A_RE + stsA + SBO, reA1);
-          sts_v4(base + OFF_A_IM + stsA, imA0);
-          sts_v4(base + OFF_A_IM + stsA + SBO, imA1);
-          sts_v4(base + OFF_B_IM + stsB, imB0);
-          sts_v4(base + OFF_B_IM + stsB + 4 * SBO, imB1);
-          sts_v4(base + OFF_B_RE + stsB, reB0);
-          sts_v4(base + OFF_B_RE + stsB + 4 * SBO, reB1);
-          sts_v4(base + OFF_B_NIM + stsB, nimB0);
-          sts_v4(base + OFF_B_NIM + stsB + 4 * SBO, nimB1);
+        {
+          // The TMA warp may refill the raw slot once the loads have RETURNED, not merely issued (SYNCS.ARRIVE does
+          // not wait for outstanding LDS): make the arrive depend on one word of every load.
+          uint32_t dep = 0;
+#pragma unroll
+          for (int j = 0; j < KB; ++j)
+            if (j < nkb) dep ^= rawA[j][0].x ^ rawA[j][1].x ^ rawB[j][0].x ^ rawB[j][1].x;
+          mbar_arrive_after(&S->raw_empty[rs], scratch, dep);
         }
-        if (wg == 0 && lane == 0) XTRACE(grp, 24);
+        const uint32_t base = stages0 + slot * STAGE_BYTES;
+#pragma unroll
+        for (int j = 0; j < KB; ++j) {
+          if (j < nkb) {
+            const uint4 colB0 = parity_lo(rawB[j][0], rawB[j][1]), colB1 = parity_hi(rawB[j][0], rawB[j][1]);
+            uint4 reA0, imA0, reA1, imA1, reB0, imB0, reB1, imB1, nimB0, nimB1;
+            if (ABL && (ablate & 16)) {
+              reA0 = imA0 = rawA[j][0]; reA1 = imA1 = rawA[j][1];
+              reB0 = imB0 = nimB0 = colB0; reB1 = imB1 = nimB1 = colB1;
+            } else {
+              reA0 = re16(rawA[j][0]); imA0 = im16(rawA[j][0]); reA1 = re16(rawA[j][1]); imA1 = im16(rawA[j][1]);
+              reB0 = re16(colB0); imB0 = im16(colB0); reB1 = re16(colB1); imB1 = im16(colB1);
+              nimB0 = neg16(imB0); nimB1 = neg16(imB1);
+            }
+            if (j == 0) {
+              XTRACE(grp, 2);
+              mbar_wait(&S->empty[slot], ((gs / NSTAGE) & 1) ^ 1, a.err, 200 + slot);
+              XTRACE(grp, 3);
+            }
+            if (!(ablate & 8)) {
+              const uint32_t bj = base + j * (4 * KGRP_BYTES);
+              sts_v4(bj + OFF_A_RE + stsA, reA0);
+              sts_v4(bj + OFF_A_RE + stsA + SBO, reA1);
+              sts_v4(bj + OFF_A_IM + stsA, imA0);
+              sts_v4(bj + OFF_A_IM + stsA + SBO, imA1);
+              sts_v4(bj + OFF_B_IM + stsB, imB0);
+              sts_v4(bj + OFF_B_IM + stsB + 4 * SBO, imB1);
+              sts_v4(bj + OFF_B_RE + stsB, reB0);
+              sts_v4(bj + OFF_B_RE + stsB + 4 * SBO, reB1);
+              sts_v4(bj + OFF_B_NIM + stsB, nimB0);
+              sts_v4(bj + OFF_B_NIM + stsB + 4 * SBO, nimB1);
+            }
+          }
+        }
+        XTRACE(grp, 4);
         fence_proxy_async_smem();
-        if (wg == 0 && lane == 0) XTRACE(grp, 25);
+        XTRACE(grp, 5);
         mbar_arrive(&S->full[slot]);
       }
     }
+    if (wg == 0 && lane == 0) XTRACE_DUMP(grp);
   } else if (warp == WARP_TMA) {
     // ===================================================================== TMA producer (one lane)
     if (lane == 0) {
@@ -291,9 +346,9 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
         const bool diag = (tl.I == tl.J);
         for (int ks = 0; ks < n_kstage; ++ks, ++gs) {
           const int rs = gs % RAW_STAGES;
-          XTRACE(3, 30);
+          XTRACE(3, 0);
           mbar_wait(&S->raw_empty[rs], ((gs / RAW_STAGES) & 1) ^ 1, a.err, 600 + rs);
-          XTRACE(3, 31);
+          XTRACE(3, 1);
           const uint32_t dst = smem_u32(raw + rs * RAW_STAGE_BYTES);
           if (ABL && (ablate & 32)) { mbar_arrive(&S->raw_full[rs]); continue; }
           mbar_arrive_expect_tx(&S->raw_full[rs], diag ? RAW_PANEL : RAW_STAGE_BYTES);
@@ -301,6 +356,7 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
           if (!diag) tma_load_3d(dst + RAW_PANEL, &tmap, &S->raw_full[rs], tl.J * TILE, tl.c, ks * ST_T);
         }
       }
+      XTRACE_DUMP(3);
     }
   } else {
     // ===================================================================== MMA issuer (one lane)
@@ -308,30 +364,38 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
       int gs = 0, it = 0;
       for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
         const int buf = it & 1;
-        XTRACE(2, 40);
+        XTRACE(2, 0);
         mbar_wait(&S->tmem_empty[buf], ((it >> 1) & 1) ^ 1, a.err, 300 + buf);
-        XTRACE(2, 41);
+        XTRACE(2, 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + buf * 256;
         for (int ks = 0; ks < n_kstage; ++ks, ++gs) {
           const int slot = gs % NSTAGE;
-          XTRACE(2, 42);
+          XTRACE(2, 2);
           mbar_wait(&S->full[slot], (gs / NSTAGE) & 1, a.err, 400 + slot);
-          XTRACE(2, 43);
+          XTRACE(2, 3);
           tc_fence_after();
           const uint32_t sbase = smem_u32(stages + slot * STAGE_BYTES);
+          const int nkb = min(KB, (a.ntime - ks * ST_T + 31) >> 5);
           if (!(ablate & 4)) {
             // [ re1 re0 | -re1 im0 ] += A_re x [B_re | B_nim]^T ;  [ im1 im0 | im1 re0 ] += A_im x [B_im | B_re]^T
-            umma_i8_ss(tmem_d, umma_smem_desc(sbase + OFF_A_RE, KGRP_BYTES, SBO),
-                       umma_smem_desc(sbase + OFF_B_RE, KGRP_BYTES, SBO), IDESC, ks != 0);
-            umma_i8_ss(tmem_d, umma_smem_desc(sbase + OFF_A_IM, KGRP_BYTES, SBO),
-                       umma_smem_desc(sbase + OFF_B_IM, KGRP_BYTES, SBO), IDESC, 1);
+#pragma unroll
+            for (int j = 0; j < KB; ++j) {
+              if (j < nkb) {
+                const uint32_t sj = sbase + j * (4 * KGRP_BYTES);
+                umma_i8_ss(tmem_d, umma_smem_desc(sj + OFF_A_RE, KGRP_BYTES, SBO),
+                           umma_smem_desc(sj + OFF_B_RE, KGRP_BYTES, SBO), IDESC, (ks | j) != 0);
+                umma_i8_ss(tmem_d, umma_smem_desc(sj + OFF_A_IM, KGRP_BYTES, SBO),
+                           umma_smem_desc(sj + OFF_B_IM, KGRP_BYTES, SBO), IDESC, 1);
+              }
+            }
           }
           umma_commit(&S->empty[slot]);
-          XTRACE(2, 44);
+          XTRACE(2, 4);
           if (ks == n_kstage - 1) umma_commit(&S->tmem_full[buf]);
         }
       }
+      XTRACE_DUMP(2);
     }
   }
 
@@ -345,6 +409,11 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+bool corr_tma_supported(const CorrArgs& a) {
+  return (a.ninput % 16 == 0) && ((reinterpret_cast<uintptr_t>(a.in) & 15) == 0) &&
+         ((reinterpret_cast<uintptr_t>(a.out) & 15) == 0);
+}
 
 cudaError_t launch_corr_swz(const CorrArgs& a, int nsm, cudaStream_t stream) {
   static EncodeTiledFn encode = nullptr;

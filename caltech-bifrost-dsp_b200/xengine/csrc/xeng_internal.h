@@ -22,12 +22,8 @@ struct CorrArgs {
 int corr_tc_smem_bytes();
 cudaError_t launch_corr_tc(const CorrArgs& a, int nsm, cudaStream_t stream);
 cudaError_t launch_corr_simt(const CorrArgs& a, cudaStream_t stream);
-// TMA-fed tensor-core kernel (xeng_corr2.cu): needs ninput % 16 == 0 and 16-byte aligned buffers
+// TMA-fed tensor-core kernel (xeng_corr_tma.cu): needs ninput % 16 == 0 and 16-byte aligned buffers; the default
 bool corr_tma_supported(const CorrArgs& a);
-cudaError_t launch_corr_tma(const CorrArgs& a, int nsm, cudaStream_t stream);
-// plane-split TMA-fed tensor-core kernel (xeng_corr3.cu): same requirements as the TMA kernel
-cudaError_t launch_corr_planes(const CorrArgs& a, int nsm, cudaStream_t stream);
-// swizzled-raw plane-split kernel (xeng_corr4.cu): same requirements; the default
 cudaError_t launch_corr_swz(const CorrArgs& a, int nsm, cudaStream_t stream);
 
 // bandwidth kernels (xeng_vis.cu)

@@ -20,6 +20,15 @@ __device__ __forceinline__ void mbar_fence_init() {
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// arrive that is ordered after the producers of `dep`: the value is first stored to a scratch word (the store cannot
+// issue before its source register holds the data, i.e. before the loads feeding `dep` have returned), and a warp issues
+// in program order, so the arrive follows.  Used to hand a buffer back only after LDS *data* has left it.
+__device__ __forceinline__ void mbar_arrive_after(uint64_t* bar, uint32_t scratch_saddr, uint32_t dep) {
+  asm volatile(
+      "st.shared.u32 [%1], %2;\n\t"
+      "mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)), "r"(scratch_saddr), "r"(dep)
+      : "memory");
+}
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(

@@ -38,8 +38,8 @@ typedef struct xeng_corr_s* xeng_corr_t;
 int xeng_corr_create(xeng_corr_t* h, int nstand, int npol, int nchan, int ntime_gulp, int gpu);
 int xeng_corr_destroy(xeng_corr_t h);
 int xeng_corr_set_stream(xeng_corr_t h, void* cuda_stream);
-/* 0 = tcgen05 tensor-core kernel (default: plane-split TMA-fed when the shape allows, else register-fed),
- * 1 = CUDA-core cross-check kernel (tests, Corr(test=True)), 2 = register-fed tcgen05, 3 = interleaved-panel TMA tcgen05. */
+/* 0 = tcgen05 tensor-core kernel (default: TMA-fed when ninput % 16 == 0 and buffers are 16-byte aligned, else
+ * register-fed), 1 = CUDA-core cross-check kernel (tests, Corr(test=True)), 2 = register-fed tcgen05. */
 int xeng_corr_set_impl(xeng_corr_t h, int impl);
 /* int32 words per plane: nchan*(nstand/2+1)*(nstand/4)*npol*npol*4 -- corr_block.py:231.
  * The output buffer holds 2*matlen int32: real plane, then imaginary plane. */

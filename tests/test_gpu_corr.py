@@ -41,7 +41,7 @@ def _run_corr(torch, v, impl=0, ngulp=1):
     return res
 
 
-@pytest.mark.parametrize("impl", [1, 2, 3, 0])   # CUDA-core check, register-fed / interleaved TMA / plane-split TMA (default) tcgen05
+@pytest.mark.parametrize("impl", [1, 2, 0])   # CUDA-core check, register-fed tcgen05, TMA-fed tcgen05 (default)
 @pytest.mark.parametrize("shape", [
     (16, 2, 4), (37, 3, 8), (32, 1, 64), (50, 3, 68), (480, 2, 352), (96, 5, 128), (17, 2, 12),
 ])
@@ -65,7 +65,7 @@ def test_corr_extreme_values(torch_cuda):
     assert not _run_corr(torch_cuda, v).any()
 
 
-@pytest.mark.parametrize("impl", [1, 2, 3, 0])   # CUDA-core check, register-fed / interleaved TMA / plane-split TMA (default) tcgen05
+@pytest.mark.parametrize("impl", [1, 2, 0])   # CUDA-core check, register-fed tcgen05, TMA-fed tcgen05 (default)
 def test_corr_multi_gulp_dump_and_clear(torch_cuda, impl):
     """xGPU semantics (corr_block.py:445): integrate over calls, write on doDump, clear afterwards."""
     from xengine import ops
