@@ -79,20 +79,46 @@ static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 
 constexpr uint32_t IDESC = umma_idesc(2, 1, 1, 1, 1, 128, 256);
 
+// Tile order inside a channel: r = I*(I+1)/2 + J (J <= I).  (I, J) come from a constant table and (channel, r) are
+// walked incrementally, so that every value derived from the tile index is computed on the uniform datapath (no
+// division / sqrt): with the warp index taken from %warpid this keeps the bulk-copy operands in uniform registers.
+constexpr int MAX_T = 64;                                  // row blocks: ninput <= 8192
+constexpr int MAX_TPC = MAX_T * (MAX_T + 1) / 2;
+__constant__ uint8_t c_tile_I[MAX_TPC];
+__constant__ uint8_t c_tile_J[MAX_TPC];
+
 struct Tile {
   int c, I, J;
 };
-__device__ __forceinline__ Tile decode_tile(int tile, int tiles_per_chan) {
-  Tile t;
-  t.c = tile / tiles_per_chan;
-  int r = tile - t.c * tiles_per_chan;
-  int I = static_cast<int>((sqrtf(8.f * r + 1.f) - 1.f) * 0.5f);
-  while ((I + 1) * (I + 2) / 2 <= r) ++I;
-  while (I * (I + 1) / 2 > r) --I;
-  t.I = I;
-  t.J = r - I * (I + 1) / 2;
-  return t;
-}
+struct TileWalk {
+  int tile, c, r;
+  __device__ __forceinline__ explicit TileWalk(const CorrArgs& a) {
+    tile = blockIdx.x;
+    c = 0;
+    r = blockIdx.x;
+    while (r >= a.tiles_per_chan) {
+      r -= a.tiles_per_chan;
+      ++c;
+    }
+  }
+  __device__ __forceinline__ bool valid(const CorrArgs& a) const { return tile < a.ntiles; }
+  __device__ __forceinline__ void next(const CorrArgs& a) {
+    tile += gridDim.x;
+    c += a.step_c;
+    r += a.step_r;
+    if (r >= a.tiles_per_chan) {
+      r -= a.tiles_per_chan;
+      ++c;
+    }
+  }
+  __device__ __forceinline__ Tile get() const {
+    Tile t;
+    t.c = c;
+    t.I = c_tile_I[r];
+    t.J = c_tile_J[r];
+    return t;
+  }
+};
 
 __device__ __forceinline__ uint4 re16(uint4 x) {
   return make_uint4(unpack_re4(x.x), unpack_re4(x.y), unpack_re4(x.z), unpack_re4(x.w));
@@ -138,7 +164,10 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
   uint8_t* stages = raw + RAW_STAGES * RAW_STAGE_BYTES;
   uint8_t* staging = stages + NSTAGE * STAGE_BYTES;
 
-  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);   // warp-uniform for ptxas
+  // Warp index through redux.sync (CREDUX writes a uniform register): ptxas then knows it is warp-uniform -- which it
+  // does not for threadIdx.x >> 5 or a shuffle -- so the role dispatch stays convergent and the bulk-copy operands
+  // of the epilogue are computed on the uniform datapath (no per-lane R2UR waterfall).
+  const int warp = static_cast<int>(__reduce_min_sync(0xffffffffu, threadIdx.x >> 5));
   const int lane = threadIdx.x & 31;
   const int n_kstage = (a.ntime + ST_T - 1) / ST_T;     // the TMA zero-fills samples past ntime
   const int ablate = ABL ? a.ablate : 0;
@@ -184,8 +213,8 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
     const uint32_t stg_w = smem_u32(staging) + warp * WARP_STAGING;
     const uint32_t my_run = stg_w + (b1 * 8 + A1l) * RUN_STRIDE + b1 * HALF_SKEW + p1 * 8;
     int it = 0;
-    for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
-      const Tile tl = decode_tile(tile, a.tiles_per_chan);
+    for (TileWalk tw(a); tw.valid(a); tw.next(a), ++it) {
+      const Tile tl = tw.get();
       const int buf = it & 1;
       XTRACE(4, 0);
       mbar_wait(&S->tmem_full[buf], (it >> 1) & 1, a.err, 100 + buf);
@@ -266,8 +295,8 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
     const uint32_t raw0 = smem_u32(raw), stages0 = smem_u32(stages);
     const uint32_t scratch = smem_u32(smem) + SCRATCH_OFF + (threadIdx.x - N_EPI_WARPS * 32) * 4;
     int gs0 = 0;                                                     // running stage index at the tile start
-    for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, gs0 += n_kstage) {
-      const Tile tl = decode_tile(tile, a.tiles_per_chan);
+    for (TileWalk tw(a); tw.valid(a); tw.next(a), gs0 += n_kstage) {
+      const Tile tl = tw.get();
       const uint32_t boff = (tl.I == tl.J) ? 0u : static_cast<uint32_t>(RAW_PANEL);   // diagonal: B raw == A raw
       for (int ks = (gs0 ^ grp) & 1; ks < n_kstage; ks += 2) {
         const int gs = gs0 + ks;
@@ -341,8 +370,8 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
     // ===================================================================== TMA producer (one lane)
     if (lane == 0) {
       int gs = 0;
-      for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
-        const Tile tl = decode_tile(tile, a.tiles_per_chan);
+      for (TileWalk tw(a); tw.valid(a); tw.next(a)) {
+        const Tile tl = tw.get();
         const bool diag = (tl.I == tl.J);
         for (int ks = 0; ks < n_kstage; ++ks, ++gs) {
           const int rs = gs % RAW_STAGES;
@@ -362,7 +391,7 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
     // ===================================================================== MMA issuer (one lane)
     if (lane == 0) {
       int gs = 0, it = 0;
-      for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
+      for (TileWalk tw(a); tw.valid(a); tw.next(a), ++it) {
         const int buf = it & 1;
         XTRACE(2, 0);
         mbar_wait(&S->tmem_empty[buf], ((it >> 1) & 1) ^ 1, a.err, 300 + buf);
@@ -411,11 +440,12 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 bool corr_tma_supported(const CorrArgs& a) {
-  return (a.ninput % 16 == 0) && ((reinterpret_cast<uintptr_t>(a.in) & 15) == 0) &&
+  return (a.ninput % 16 == 0) && (a.ninput <= MAX_T * TILE) && ((reinterpret_cast<uintptr_t>(a.in) & 15) == 0) &&
          ((reinterpret_cast<uintptr_t>(a.out) & 15) == 0);
 }
 
-cudaError_t launch_corr_swz(const CorrArgs& a, int nsm, cudaStream_t stream) {
+cudaError_t launch_corr_swz(const CorrArgs& a_in, int nsm, cudaStream_t stream) {
+  CorrArgs a = a_in;
   static EncodeTiledFn encode = nullptr;
   static bool configured = false;
   if (!configured) {
@@ -429,10 +459,21 @@ cudaError_t launch_corr_swz(const CorrArgs& a, int nsm, cudaStream_t stream) {
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(corr_swz_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) return e;
+    static uint8_t tab_i[MAX_TPC], tab_j[MAX_TPC];   // r = I*(I+1)/2 + J  ->  (I, J); the same for every shape
+    for (int I = 0, r = 0; I < MAX_T; ++I)
+      for (int J = 0; J <= I; ++J, ++r) {
+        tab_i[r] = static_cast<uint8_t>(I);
+        tab_j[r] = static_cast<uint8_t>(J);
+      }
+    e = cudaMemcpyToSymbol(c_tile_I, tab_i, sizeof(tab_i));
+    if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_tile_J, tab_j, sizeof(tab_j));
+    if (e != cudaSuccess) return e;
     configured = true;
   }
   int grid = a.ntiles < nsm ? a.ntiles : nsm;
   if (grid <= 0) return cudaSuccess;
+  a.step_c = grid / a.tiles_per_chan;
+  a.step_r = grid % a.tiles_per_chan;
   alignas(64) CUtensorMap tmap;
   const cuuint64_t gdim[3] = {static_cast<cuuint64_t>(a.ninput), static_cast<cuuint64_t>(a.nchan),
                               static_cast<cuuint64_t>(a.ntime)};

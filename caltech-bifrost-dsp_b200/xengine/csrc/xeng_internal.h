@@ -12,6 +12,7 @@ struct CorrArgs {
   int ntime, nchan, ninput;
   int npairs;           // nstand / 2 (station pairs)
   int tiles_per_chan, ntiles;
+  int step_c, step_r;   // grid / tiles_per_chan, grid % tiles_per_chan (filled by the TMA kernel's launcher)
   int accumulate;       // 0: out = X, 1: out += X
   int ablate;           // profiling ablation mask (XENG_CORR_ABLATE, results invalid when != 0)
   long long* trace;     // developer timeline buffer (XENG_CORR_TRACE), null in production
