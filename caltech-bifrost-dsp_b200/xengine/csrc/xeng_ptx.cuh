@@ -40,16 +40,34 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: a protocol bug must not hang the GPU (a hung box is a strike); after
-// ~4 s of spinning the kernel records the barrier id in *err and traps.
+// try_wait with a suspend-time hint (ns): the thread sleeps in hardware until the phase completes or the hint expires,
+// instead of burning issue slots that the working warps of the same SM sub-partition need.
+__device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parity, uint32_t hint_ns) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(hint_ns)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait: a protocol bug must not hang the GPU (a hung box is a strike); after ~4 s of waiting the kernel
+// records the barrier id in *err and traps.  The clock is only consulted every 256 unsuccessful probes.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int* err, int tag) {
   if (mbar_try_wait(bar, parity)) return;
-  long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 8000000000LL) {
-      if (err) atomicExch(err, tag);
-      __threadfence_system();
-      asm volatile("trap;");
+  uint32_t probes = 0;
+  long long t0 = 0;
+  while (!mbar_try_wait_hint(bar, parity, 20000u)) {
+    if ((++probes & 255u) == 0) {
+      const long long now = clock64();
+      if (t0 == 0) t0 = now;
+      if (now - t0 > 8000000000LL) {
+        if (err) atomicExch(err, tag);
+        __threadfence_system();
+        asm volatile("trap;");
+      }
     }
   }
 }
