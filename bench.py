@@ -43,6 +43,7 @@ def parse():
     p.add_argument("--acc-gulps", type=int, default=250)
     p.add_argument("--cpu-seconds", type=float, default=15.0, help="budget for the cpu_baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-path-kernels", action="store_true", help="skip the per-kernel figures of the rest of the path")
     return p.parse_args()
 
 
@@ -172,6 +173,82 @@ class ClockSampler(object):
             out["samples"] = len(sm)
         out["reasons"] = sorted(reasons)
         return out
+
+
+# ----------------------------------------------------------------------------------------------
+# the other kernels of the path: bandwidth / flop figures next to the headline kernel
+# ----------------------------------------------------------------------------------------------
+def ncu_traffic(nchan, ntime):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one fused Corr+CorrAcc launch, from the committed ncu
+    --set full capture (profiles/corr_traffic.json, written by scripts/summarize_ncu.py)."""
+    path = os.path.join(ROOT, "profiles", "corr_traffic.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            d = json.load(f)
+        if d.get("nchan") == nchan and d.get("ntime_gulp") == ntime:     # captured on this workload only
+            return float(d["dram_bytes_per_launch"]), d.get("source")
+    return None, None
+
+
+def path_kernels(torch, ops, dev, nchan, hbm_peak, iters=10):
+    """CUDA-event timings (L2 flushed between launches) of CorrAcc, CorrSubsel, reorder, Beamform and BeamformSum at
+    the sizes of BASELINE configs[1]/[3]/[4]; algorithmic bytes / flops per SURVEY 8(d)."""
+    flush = torch.zeros(256 << 20, dtype=torch.uint8, device=dev)
+
+    def timeit(fn, n=iters):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize(dev)
+        ts = []
+        for _ in range(n):
+            flush.add_(1)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize(dev)
+            ts.append(e0.elapsed_time(e1))
+        return float(np.median(ts))
+
+    res = {}
+    wpc = ops.words_per_chan(NSTAND)
+    nw = 2 * nchan * wpc
+    vis = torch.randint(-1000, 1000, (nw,), dtype=torch.int32, device=dev)
+    acc = torch.zeros(nw, dtype=torch.int32, device=dev)
+    ms = timeit(lambda: ops.acc(acc, vis, nw, False))
+    res["corr_acc"] = {"ms": ms, "alg_bytes": 12 * nw, "gbs": 12 * nw / ms / 1e6, "frac_hbm": 12 * nw / ms / 1e6 / hbm_peak}
+    a2i = np.arange(NINPUT, dtype=np.int32).reshape(NSTAND, NPOL)
+    a2bl, conj = ops.get_order(a2i)
+    for nvis in (4704, 4656):
+        sel = np.random.default_rng(nvis).integers(0, a2bl.size, nvis)
+        vm = torch.from_numpy(a2bl.reshape(-1)[sel].copy()).to(dev)
+        cj = torch.from_numpy(conj.reshape(-1)[sel].copy()).to(dev)
+        so = torch.zeros((nchan // 4, nvis, 2), dtype=torch.int32, device=dev)
+        ms = timeit(lambda: ops.subsel(vis, so, vm, cj, nvis, nchan, 4, wpc))
+        ab = 8 * nvis * nchan + 8 * nvis * nchan // 4
+        res["corr_subsel_%d" % nvis] = {"ms": ms, "alg_bytes": ab, "gbs": ab / ms / 1e6,
+                                        "sector_bytes": 2 * 32 * nvis * nchan + 8 * nvis * nchan // 4}
+    ro = torch.zeros((NSTAND, NSTAND, 2, 2, nchan, 2), dtype=torch.int32, device=dev)
+    da, dc = torch.from_numpy(a2bl).to(dev), torch.from_numpy(conj).to(dev)
+    ms = timeit(lambda: ops.reorder(vis, ro, da, dc, NSTAND, NPOL, nchan, wpc), 4)
+    ab = ro.numel() * 4 + ro.numel() * 4 // 2     # every output word written, each stored word read once
+    res["reorder"] = {"ms": ms, "alg_bytes": ab, "gbs": ab / ms / 1e6, "frac_hbm": ab / ms / 1e6 / hbm_peak}
+    del ro, vis, acc
+    nbeam, nt, nsum = 32, 960, 24
+    bf = ops.Beamformer(ninput=NINPUT, nchan=nchan, ntime=nt, nbeam=nbeam)
+    vv = torch.randint(0, 256, (nt, nchan, NINPUT), dtype=torch.uint8, device=dev)
+    w = torch.randn((nchan, nbeam, NINPUT, 2), dtype=torch.float32, device=dev)
+    bo = torch.zeros((nchan, nbeam, nt, 2), dtype=torch.float32, device=dev)
+    po = torch.zeros((nbeam // 2, nt // nsum, nchan, 4), dtype=torch.float32, device=dev)
+    ms = timeit(lambda: bf.run(vv, bo, w))
+    fl = 8.0 * nbeam * NINPUT * nchan * nt
+    res["beamform"] = {"ms": ms, "gsamples_per_s": nt * nchan * NINPUT / ms / 1e6, "tflops_fp32": fl / ms / 1e9,
+                       "config": "%d beams x %d inputs x %d ch x %d samples" % (nbeam, NINPUT, nchan, nt)}
+    ms = timeit(lambda: bf.integrate(bo, po, nsum))
+    ab = bo.numel() * 4 + po.numel() * 4
+    res["beamform_sum"] = {"ms": ms, "alg_bytes": ab, "gbs": ab / ms / 1e6, "frac_hbm": ab / ms / 1e6 / hbm_peak}
+    bf.close()
+    return res
 
 
 # ----------------------------------------------------------------------------------------------
@@ -329,6 +406,7 @@ def run_b200(args):
         except Exception:
             pass
         alg_bytes = in_bytes + 2 * out_words * 4                      # read gulp + read-modify-write accumulator
+        traffic, traffic_src = ncu_traffic(nchan, ntime)
         achieved = alg_bytes / kern_ms / 1e6
         useful_tops = OPS_PER_SAMPLE * nsamp_step / kern_ms / 1e9
         value = world * nsamp_step * K / total_ms / 1e6
@@ -343,7 +421,8 @@ def run_b200(args):
                     "ms_per_step": e2e_ms / K, "checksum": checksum},
             "gpu_launches": K,
             "roofline": {"kernel": "corr_swz_kernel (fused Corr+CorrAcc)", "bound": "hbm", "achieved": achieved,
-                         "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                         "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
+                         "traffic_source": traffic_src,
                          "peak_source": peak_src, "alg_bytes_per_launch": alg_bytes, "kernel_ms": kern_ms,
                          "tensor": {"useful_int8_tops": useful_tops, "nominal_peak_tops": INT8_NOMINAL_TOPS,
                                     "frac_nominal": useful_tops / INT8_NOMINAL_TOPS,
@@ -352,6 +431,10 @@ def run_b200(args):
             "realtime": {"required_gsps_per_%dch" % nchan: nchan * NINPUT * 23925.78125 / 1e9,
                          "full_band_required_gsps": 3072 * NINPUT * 23925.78125 / 1e9},
         }
+        if not args.no_path_kernels and world == 1:
+            del d_in, d_dump, ring
+            torch.cuda.empty_cache()
+            line["path_kernels"] = path_kernels(torch, ops, dev, nchan, hbm_peak)
         if not args.no_cpu_baseline:
             v, desc, cores, _, _ = cpu_corr_sample(nchan * world, ntime, args.cpu_seconds)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}

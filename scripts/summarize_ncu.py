@@ -70,6 +70,21 @@ def full(src, dst):
                 if h in KEYS:
                     f.write("  %-80s %s %s\n" % (h, r[i], units[i]))
     sys.stdout.write(open(dst).read())
+    # steady-state (accumulating) launch = the one that also reads the accumulator: DRAM bytes per launch for bench.py
+    def num(r, key):
+        i = hdr.index(key)
+        mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(units[i], 1.0)
+        return float(r[i].replace(",", "")) * mult
+    corr = [r for r in data if "corr_" in r[name_col]]
+    if corr and len(sys.argv) > 4:
+        r = max(corr, key=lambda r: num(r, "dram__bytes_read.sum"))
+        out = {"dram_bytes_per_launch": num(r, "dram__bytes_read.sum") + num(r, "dram__bytes_write.sum"),
+               "dram_bytes_read": num(r, "dram__bytes_read.sum"), "dram_bytes_write": num(r, "dram__bytes_write.sum"),
+               "kernel": r[name_col][:80], "nchan": 192, "ntime_gulp": 480, "source": dst,
+               "how": "ncu --set full --clock-control none, accumulating launch of `bench.py --steps 4 --warmup 3`"}
+        import json
+        with open(sys.argv[4], "w") as f:
+            json.dump(out, f, indent=1)
 
 
 if __name__ == "__main__":
