@@ -266,7 +266,13 @@ def run_b200(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    real_stdout = sys.stdout
     if world > 1:
+        # NCCL / c10d print a version banner on fd 1: keep stdout to the one JSON line by pointing fd 1 at stderr
+        # for the lifetime of the process group and writing the result to a duplicate of the original stdout.
+        sys.stdout.flush()
+        real_stdout = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
     nchan, ntime, K, Wm, accg = args.nchan_per_gpu, args.ntime, args.steps, args.warmup, args.acc_gulps
     wpc = ops.words_per_chan(NSTAND)
@@ -308,6 +314,7 @@ def run_b200(args):
     with torch.cuda.stream(stream):
         for i in range(Wm):
             step_device(i)
+        dump_device()          # warm the dump path too (first NCCL gather sets up its peer connections)
     barrier()
     sampler = ClockSampler(local) if rank == 0 else None
     evs = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
@@ -438,7 +445,8 @@ def run_b200(args):
         if not args.no_cpu_baseline:
             v, desc, cores, _, _ = cpu_corr_sample(nchan * world, ntime, args.cpu_seconds)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
-        print(json.dumps(line))
+        real_stdout.write(json.dumps(line) + "\n")
+        real_stdout.flush()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
