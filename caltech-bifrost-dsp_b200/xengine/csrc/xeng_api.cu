@@ -1,5 +1,6 @@
 // libxeng C ABI (see include/xeng.h).  Host-side glue only: argument checks, handle state, launches.
 // No CPU arithmetic path exists here: every entry point either launches a CUDA kernel or fails.
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -53,6 +54,13 @@ struct xeng_corr_s {
   int* d_err;
   uint8_t* d_stage_in; // staging for the host-memory variant
   int32_t* d_stage_out;
+  // fused CorrSubsel selection (xeng_corr_set_subsel)
+  int sub_nvis, sub_nsum;
+  int* d_sub_begin;          // [tiles_per_chan * 8 + 1]
+  uint32_t* d_sub_entries;   // [nvis] packed (staging offset | conj << 14 | v << 15), grouped by (tile, warp)
+  int32_t* d_sub_vismap;     // [nvis] device copies for the unfused fallback
+  int32_t* d_sub_conj;
+  int32_t* d_sub_scratch;    // per-gulp visibilities, unfused fallback only
 };
 
 struct xeng_bf_s {
@@ -112,6 +120,11 @@ int xeng_corr_destroy(xeng_corr_t h) {
   if (h->d_acc) cudaFree(h->d_acc);
   if (h->d_stage_in) cudaFree(h->d_stage_in);
   if (h->d_stage_out) cudaFree(h->d_stage_out);
+  if (h->d_sub_begin) cudaFree(h->d_sub_begin);
+  if (h->d_sub_entries) cudaFree(h->d_sub_entries);
+  if (h->d_sub_vismap) cudaFree(h->d_sub_vismap);
+  if (h->d_sub_conj) cudaFree(h->d_sub_conj);
+  if (h->d_sub_scratch) cudaFree(h->d_sub_scratch);
   if (h->h_err) cudaFreeHost(h->h_err);
   delete h;
   return XENG_OK;
@@ -131,7 +144,7 @@ int xeng_corr_set_impl(xeng_corr_t h, int impl) {
 }
 int64_t xeng_corr_matlen(xeng_corr_t h) { return h ? h->matlen : 0; }
 
-static int corr_launch(xeng_corr_t h, const void* d_in, int32_t* d_out, int accumulate) {
+static int corr_launch(xeng_corr_t h, const void* d_in, int32_t* d_out, int accumulate, int32_t* d_sub_out = nullptr) {
   xeng::CorrArgs a;
   a.in = static_cast<const uint8_t*>(d_in);
   a.out = d_out;
@@ -147,6 +160,8 @@ static int corr_launch(xeng_corr_t h, const void* d_in, int32_t* d_out, int accu
     a.ablate = ab ? atoi(ab) : 0;
   }
   a.trace = nullptr;
+  a.sub_begin = h->d_sub_begin; a.sub_entries = h->d_sub_entries; a.sub_out = d_sub_out;
+  a.sub_nvis = h->sub_nvis; a.sub_nsum = h->sub_nsum;
   const char* trace_path = getenv("XENG_CORR_TRACE");   // developer-only: per-role clock64 timeline of CTA 0
   static long long* d_trace = nullptr;
   const size_t trace_bytes = 5 * 4096 * 2 * sizeof(long long);
@@ -203,6 +218,99 @@ int xeng_corr_accumulate(xeng_corr_t h, const void* d_in, void* d_acc, int first
   int rc = corr_check(h, d_in, d_acc, true);
   if (rc) return rc;
   return corr_launch(h, d_in, static_cast<int32_t*>(d_acc), first ? 0 : 1);
+}
+
+static bool corr_uses_tma(xeng_corr_t h, const void* d_in, const void* d_out) {
+  xeng::CorrArgs a;
+  a.in = static_cast<const uint8_t*>(d_in);
+  a.out = static_cast<int32_t*>(const_cast<void*>(d_out));
+  a.ninput = h->ninput;
+  return h->impl == 0 && xeng::corr_tma_supported(a);
+}
+
+int xeng_corr_set_subsel(xeng_corr_t h, const int32_t* vismap, const int32_t* conj, int nvis, int nchan_sum) {
+  if (!h) return fail(XENG_ERR_ARG, "null handle");
+  XENG_CUDA(cudaSetDevice(h->device));
+  XENG_CUDA(cudaStreamSynchronize(h->stream));       // a launch may still be reading the old tables
+  if (h->d_sub_begin) { cudaFree(h->d_sub_begin); h->d_sub_begin = nullptr; }
+  if (h->d_sub_entries) { cudaFree(h->d_sub_entries); h->d_sub_entries = nullptr; }
+  if (h->d_sub_vismap) { cudaFree(h->d_sub_vismap); h->d_sub_vismap = nullptr; }
+  if (h->d_sub_conj) { cudaFree(h->d_sub_conj); h->d_sub_conj = nullptr; }
+  h->sub_nvis = 0; h->sub_nsum = 0;
+  if (nvis == 0) return XENG_OK;
+  if (!vismap || !conj) return fail(XENG_ERR_ARG, "null pointer");
+  if (nvis < 0 || nvis >= (1 << 17)) return fail(XENG_ERR_ARG, "nvis must be in [0, 131072), got %d", nvis);
+  if (nchan_sum <= 0 || h->nchan % nchan_sum) return fail(XENG_ERR_ARG, "nchan_sum must divide nchan");
+  const int T = (h->ninput + 127) / 128, tpc = T * (T + 1) / 2, nlist = tpc * 8;
+  int* begin = static_cast<int*>(calloc(nlist + 1, sizeof(int)));
+  int* key = static_cast<int*>(malloc(sizeof(int) * nvis));
+  uint32_t* packed = static_cast<uint32_t*>(malloc(sizeof(uint32_t) * nvis));
+  uint32_t* sorted = static_cast<uint32_t*>(malloc(sizeof(uint32_t) * nvis));
+  if (!begin || !key || !packed || !sorted) { free(begin); free(key); free(packed); free(sorted); return fail(XENG_ERR_NOMEM, "host allocation failed"); }
+  int rc = XENG_OK;
+  for (int v = 0; v < nvis && rc == XENG_OK; ++v) {
+    const long w = vismap[v];
+    if (w < 0 || w >= h->words_per_chan) { rc = fail(XENG_ERR_ARG, "vismap[%d] = %ld outside [0, %ld)", v, w, h->words_per_chan); break; }
+    const long cell = w >> 2, quad = cell / h->quad_cells, t = cell % h->quad_cells;
+    const int p1 = static_cast<int>((w >> 1) & 1), p0 = static_cast<int>(w & 1);
+    const int b0 = static_cast<int>(quad >> 1), b1 = static_cast<int>(quad & 1);
+    long A1 = static_cast<long>((sqrt(8.0 * static_cast<double>(t) + 1.0) - 1.0) * 0.5);
+    while ((A1 + 1) * (A1 + 2) / 2 <= t) ++A1;
+    while (A1 * (A1 + 1) / 2 > t) --A1;
+    const long A0 = t - A1 * (A1 + 1) / 2;
+    const int I = static_cast<int>(A1 / 32), J = static_cast<int>(A0 / 32), A1loc = static_cast<int>(A1 % 32);
+    const int list = (I * (I + 1) / 2 + J) * 8 + b0 * 4 + A1loc / 8;
+    key[v] = list;
+    packed[v] = static_cast<uint32_t>(xeng::corr_swz_staging_offset(A1loc, b1, p1, static_cast<int>(A0 % 32), p0)) |
+                (conj[v] ? (1u << 14) : 0u) | (static_cast<uint32_t>(v) << 15);
+    ++begin[list + 1];
+  }
+  if (rc == XENG_OK) {
+    for (int i = 0; i < nlist; ++i) begin[i + 1] += begin[i];
+    int* fill = static_cast<int*>(calloc(nlist, sizeof(int)));
+    if (!fill) rc = fail(XENG_ERR_NOMEM, "host allocation failed");
+    else {
+      for (int v = 0; v < nvis; ++v) sorted[begin[key[v]] + fill[key[v]]++] = packed[v];
+      free(fill);
+    }
+  }
+  cudaError_t e = cudaSuccess;
+  if (rc == XENG_OK) {
+    e = cudaMalloc(reinterpret_cast<void**>(&h->d_sub_begin), sizeof(int) * (nlist + 1));
+    if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&h->d_sub_entries), sizeof(uint32_t) * nvis);
+    if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&h->d_sub_vismap), sizeof(int32_t) * nvis);
+    if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&h->d_sub_conj), sizeof(int32_t) * nvis);
+    if (e == cudaSuccess) e = cudaMemcpy(h->d_sub_begin, begin, sizeof(int) * (nlist + 1), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(h->d_sub_entries, sorted, sizeof(uint32_t) * nvis, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(h->d_sub_vismap, vismap, sizeof(int32_t) * nvis, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(h->d_sub_conj, conj, sizeof(int32_t) * nvis, cudaMemcpyHostToDevice);
+  }
+  free(begin); free(key); free(packed); free(sorted);
+  if (rc != XENG_OK) return rc;
+  if (e != cudaSuccess) return fail(XENG_ERR_CUDA, "xeng_corr_set_subsel: %s", cudaGetErrorString(e));
+  h->sub_nvis = nvis; h->sub_nsum = nchan_sum;
+  return XENG_OK;
+}
+
+int xeng_corr_accumulate_subsel(xeng_corr_t h, const void* d_in, void* d_acc, int first, void* d_sub_out) {
+  int rc = corr_check(h, d_in, d_acc, true);
+  if (rc) return rc;
+  if (!d_sub_out) return fail(XENG_ERR_ARG, "null sub-select output pointer");
+  if (h->sub_nvis <= 0) return fail(XENG_ERR_ARG, "no selection set: call xeng_corr_set_subsel first");
+  int32_t* so = static_cast<int32_t*>(d_sub_out);
+  if (corr_uses_tma(h, d_in, d_acc)) {   // one launch: correlate, accumulate in L2, sub-select from the staging buffers
+    XENG_CUDA(cudaMemsetAsync(so, 0, sizeof(int32_t) * 2 * h->sub_nvis * (h->nchan / h->sub_nsum), h->stream));
+    return corr_launch(h, d_in, static_cast<int32_t*>(d_acc), first ? 0 : 1, so);
+  }
+  // shapes the TMA kernel cannot take: per-gulp visibilities into a scratch buffer, then the stand-alone kernels
+  const size_t words = static_cast<size_t>(2 * h->matlen);
+  if (!h->d_sub_scratch) XENG_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->d_sub_scratch), words * sizeof(int32_t)));
+  rc = corr_launch(h, d_in, h->d_sub_scratch, 0);
+  if (rc) return rc;
+  XENG_CUDA(xeng::launch_acc(static_cast<int32_t*>(d_acc), h->d_sub_scratch, words, first ? 1 : 0, h->stream));
+  XENG_CUDA(xeng::launch_subsel(h->d_sub_scratch, so, h->d_sub_vismap, h->d_sub_conj, h->sub_nvis, h->nchan,
+                                h->sub_nsum, h->words_per_chan, h->stream));
+  return XENG_OK;
 }
 
 int xeng_corr_sync(xeng_corr_t h) {

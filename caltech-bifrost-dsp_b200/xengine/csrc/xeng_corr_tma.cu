@@ -155,7 +155,7 @@ __device__ __forceinline__ uint4 parity_hi(uint4 a, uint4 b) {
       for (int i__ = 0; i__ < 8; ++i__) a.trace[(role) * 8 + i__] = tacc[i__];             \
   } while (0)
 
-template <bool ABL>
+template <bool ABL, bool SUB>
 __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_constant__ CUtensorMap tmap, CorrArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -277,6 +277,18 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
           }
         }
         bulk_commit();
+        if (SUB) {
+          // fused CorrSubsel (corr_subsel_block.py:298): the selected words of this warp's 16 runs, straight from the
+          // staging buffer; the nchan_sum channels of one output row come from different tiles -> red.global.add
+          const int lb = a.sub_begin[tw.r * N_EPI_WARPS + warp], le = a.sub_begin[tw.r * N_EPI_WARPS + warp + 1];
+          int32_t* const so = a.sub_out + (static_cast<long>(tl.c / a.sub_nsum) * a.sub_nvis) * 2 + plane;
+          for (int e = lb + lane; e < le; e += 32) {
+            const uint32_t en = a.sub_entries[e];
+            int val = static_cast<int>(lds_u32(stg_w + (en & 0x3FFFu)));
+            if (plane == 1 && ((en >> 14) & 1u)) val = -val;          // imaginary part negated where conj[v]
+            atomicAdd(so + static_cast<long>(en >> 15) * 2, val);      // result unused -> RED.ADD
+          }
+        }
         XTRACE(4, 7);
       }
     }
@@ -439,6 +451,11 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+int corr_swz_staging_offset(int A1loc, int b1, int p1, int a0, int p0) {
+  // must match the epilogue: lane (A1loc & 7, b1, p1) writes {column 2*a0, 2*a0+1} at my_run + a0*16
+  return (b1 * 8 + (A1loc & 7)) * RUN_STRIDE + b1 * HALF_SKEW + p1 * 8 + a0 * 16 + p0 * 4;
+}
+
 bool corr_tma_supported(const CorrArgs& a) {
   return (a.ninput % 16 == 0) && (a.ninput <= MAX_T * TILE) && ((reinterpret_cast<uintptr_t>(a.in) & 15) == 0) &&
          ((reinterpret_cast<uintptr_t>(a.out) & 15) == 0);
@@ -455,9 +472,11 @@ cudaError_t launch_corr_swz(const CorrArgs& a_in, int nsm, cudaStream_t stream) 
     if (e != cudaSuccess) return e;
     if (qres != cudaDriverEntryPointSuccess || !fn) return cudaErrorNotSupported;
     encode = reinterpret_cast<EncodeTiledFn>(fn);
-    e = cudaFuncSetAttribute(corr_swz_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    e = cudaFuncSetAttribute(corr_swz_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(corr_swz_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+      e = cudaFuncSetAttribute(corr_swz_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(corr_swz_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) return e;
     static uint8_t tab_i[MAX_TPC], tab_j[MAX_TPC];   // r = I*(I+1)/2 + J  ->  (I, J); the same for every shape
     for (int I = 0, r = 0; I < MAX_T; ++I)
@@ -485,8 +504,9 @@ cudaError_t launch_corr_swz(const CorrArgs& a_in, int nsm, cudaStream_t stream) 
                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
-  if (a.ablate) corr_swz_kernel<true><<<grid, N_THREADS, SMEM_BYTES, stream>>>(tmap, a);
-  else corr_swz_kernel<false><<<grid, N_THREADS, SMEM_BYTES, stream>>>(tmap, a);
+  if (a.sub_out) corr_swz_kernel<false, true><<<grid, N_THREADS, SMEM_BYTES, stream>>>(tmap, a);
+  else if (a.ablate) corr_swz_kernel<true, false><<<grid, N_THREADS, SMEM_BYTES, stream>>>(tmap, a);
+  else corr_swz_kernel<false, false><<<grid, N_THREADS, SMEM_BYTES, stream>>>(tmap, a);
   return cudaGetLastError();
 }
 

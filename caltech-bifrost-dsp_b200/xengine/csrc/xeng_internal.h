@@ -18,6 +18,13 @@ struct CorrArgs {
   long long* trace;     // developer timeline buffer (XENG_CORR_TRACE), null in production
   long words_per_chan;  // (nstand/2+1)*(nstand/4)*16
   long quad_cells;      // (nstand/2+1)*(nstand/4): cells per xGPU quadrant
+  // fused CorrSubsel (TMA kernel only; sub_out == nullptr: off).  For tile-in-channel r and epilogue warp w the entries
+  // sub_entries[sub_begin[r*8+w] .. sub_begin[r*8+w+1]) name the selected words that warp stages:
+  // bits 0..13 byte offset in the warp's staging buffer, bit 14 conjugate, bits 15.. index v of the selection.
+  const int* sub_begin;
+  const uint32_t* sub_entries;
+  int32_t* sub_out;     // [nchan / sub_nsum][sub_nvis][2], zeroed by the launcher, accumulated with red.global.add
+  int sub_nvis, sub_nsum;
 };
 
 int corr_tc_smem_bytes();
@@ -26,6 +33,8 @@ cudaError_t launch_corr_simt(const CorrArgs& a, cudaStream_t stream);
 // TMA-fed tensor-core kernel (xeng_corr_tma.cu): needs ninput % 16 == 0 and 16-byte aligned buffers; the default
 bool corr_tma_supported(const CorrArgs& a);
 cudaError_t launch_corr_swz(const CorrArgs& a, int nsm, cudaStream_t stream);
+// staging-buffer geometry of the TMA kernel's epilogue, for the host-side sub-select table (xeng_api.cu)
+int corr_swz_staging_offset(int A1loc, int b1, int p1, int a0, int p0);
 
 // bandwidth kernels (xeng_vis.cu)
 cudaError_t launch_acc(int32_t* acc, const int32_t* in, size_t n, int first, cudaStream_t stream);

@@ -46,6 +46,23 @@ class XCorr(object):
         """Fused Corr + CorrAcc step: d_acc (=|+=) X(d_in)."""
         check(self._lib.xeng_corr_accumulate(self._h, ptr(d_in), ptr(d_acc), int(bool(first))), "xeng_corr_accumulate")
 
+    def set_subsel(self, vismap, conj, nchan_sum=4):
+        """Selection for the fused fast-dump path: the host arrays CorrSubsel.update_subsel builds
+        (corr_subsel_block.py:237-250).  An empty selection clears it."""
+        vm = np.ascontiguousarray(vismap, dtype=np.int32)
+        cj = np.ascontiguousarray(conj, dtype=np.int32)
+        if vm.shape != cj.shape or vm.ndim != 1:
+            raise ValueError("vismap and conj must be 1-D arrays of the same length")
+        check(self._lib.xeng_corr_set_subsel(self._h, ptr(vm), ptr(cj), int(vm.size), int(nchan_sum)),
+              "xeng_corr_set_subsel")
+        self.nvis, self.nchan_sum = int(vm.size), int(nchan_sum)
+
+    def accumulate_subsel(self, d_in, d_acc, first, d_sub_out):
+        """Fused Corr + CorrAcc + CorrSubsel step: d_acc (=|+=) X(d_in); d_sub_out[nchan/nchan_sum][nvis][2] = this
+        gulp's selected visibilities summed over nchan_sum channels."""
+        check(self._lib.xeng_corr_accumulate_subsel(self._h, ptr(d_in), ptr(d_acc), int(bool(first)), ptr(d_sub_out)),
+              "xeng_corr_accumulate_subsel")
+
     def sync(self):
         check(self._lib.xeng_corr_sync(self._h), "xeng_corr_sync")
 

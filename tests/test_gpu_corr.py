@@ -209,3 +209,74 @@ def test_subsel_and_reorder(torch_cuda):
         for k, ((s0, p0), (s1, p1)) in enumerate(bls[:50]):
             assert np.array_equal(got[:, k, 0], fre[:, s0, s1, p0, p1].reshape(-1, ncs).sum(1))
             assert np.array_equal(got[:, k, 1], fim[:, s0, s1, p0, p1].reshape(-1, ncs).sum(1))
+
+
+@pytest.mark.parametrize("shape,ncs,impl", [
+    ((96, 8, 64), 4, 0),     # TMA kernel, several tiles per channel
+    ((130, 4, 68), 2, 0),    # ragged last row block, K not a multiple of the stage
+    ((40, 8, 12), 4, 0),     # ninput = 24: not a multiple of 16 -> unfused fallback inside the library
+    ((64, 4, 36), 1, 2),     # register-fed kernel -> unfused fallback
+])
+def test_corr_fused_accumulate_subsel(torch_cuda, shape, ncs, impl):
+    """BASELINE configs[4]: Corr + CorrAcc + CorrSubsel in one call; accumulator and fast dump both bit-exact."""
+    from xengine import ops
+    torch = torch_cuda
+    nt, nchan, nstand = shape
+    rng = np.random.default_rng(99 + nstand)
+    a2bl, conj = ops.get_order(np.arange(nstand * 2, dtype=np.int32).reshape(nstand, 2))
+    # default selection of the reference (pol-0 autos, corr_subsel_block.py:230) + random baselines in both orders
+    bls = [[[i % nstand, 0], [i % nstand, 0]] for i in range(48)]
+    bls += [[[int(rng.integers(nstand)), int(rng.integers(2))], [int(rng.integers(nstand)), int(rng.integers(2))]]
+            for _ in range(700)]
+    vm, cj = orc.baselines_to_vismap(bls, a2bl, conj)
+    xc = ops.XCorr(nstand=nstand, nchan=nchan, ntime_gulp=nt)
+    xc.set_impl(impl)
+    xc.set_subsel(vm, cj, ncs)
+    wpc = ops.words_per_chan(nstand)
+    acc = torch.full((2, nchan, wpc), 7, dtype=torch.int32, device="cuda")
+    fast = torch.full((nchan // ncs, len(bls), 2), -5, dtype=torch.int32, device="cuda")
+    want_acc = np.zeros((2, nchan, wpc), dtype=np.int64)
+    for g in range(3):
+        v = _voltages(rng, nt, nchan, nstand)
+        x = orc.corr_xgpu(v)
+        want_acc += x
+        xc.accumulate_subsel(torch.from_numpy(v).cuda(), acc, g == 0, fast)
+        xc.sync()
+        assert np.array_equal(fast.cpu().numpy(), orc.subselect(x, vm, cj, ncs)), "fast dump of gulp %d" % g
+        assert np.array_equal(acc.cpu().numpy(), want_acc.astype(np.int32)), "accumulator after gulp %d" % g
+    xc.set_subsel(np.zeros(0, np.int32), np.zeros(0, np.int32), ncs)     # cleared: the call must refuse
+    with pytest.raises(Exception):
+        xc.accumulate_subsel(torch.from_numpy(v).cuda(), acc, False, fast)
+    xc.close()
+
+
+def test_corr_fused_subsel_full_size(torch_cuda):
+    """704 inputs x 192 channels x 480 samples, 4704 and 4656 baselines, nchan_sum = 4: the fused fast dump equals the
+    stand-alone CorrSubsel kernel run on the stand-alone Corr output (device-side cross-check at BASELINE size)."""
+    from xengine import ops
+    torch = torch_cuda
+    nt, nchan, nstand = 480, 192, 352
+    rng = np.random.default_rng(5)
+    a2bl, conj = ops.get_order(np.arange(nstand * 2, dtype=np.int32).reshape(nstand, 2))
+    wpc = ops.words_per_chan(nstand)
+    v = torch.randint(0, 256, (nt, nchan, nstand * 2), dtype=torch.uint8, device="cuda")
+    xc = ops.XCorr(nstand=nstand, nchan=nchan, ntime_gulp=nt)
+    ref = torch.zeros((2, nchan, wpc), dtype=torch.int32, device="cuda")
+    xc.run(v, ref, True)
+    xc.sync()
+    for nvis in (4704, 4656):
+        sel = rng.integers(0, a2bl.size, nvis)
+        vm, cj = a2bl.reshape(-1)[sel].copy(), conj.reshape(-1)[sel].copy()
+        xc.set_subsel(vm, cj, 4)
+        acc = torch.zeros((2, nchan, wpc), dtype=torch.int32, device="cuda")
+        fast = torch.zeros((nchan // 4, nvis, 2), dtype=torch.int32, device="cuda")
+        xc.accumulate_subsel(v, acc, True, fast)
+        xc.accumulate_subsel(v, acc, False, fast)
+        xc.sync()
+        want = torch.zeros_like(fast)
+        ops.subsel(ref, want, torch.from_numpy(vm).cuda(), torch.from_numpy(cj).cuda(), nvis, nchan, 4, wpc)
+        torch.cuda.synchronize()
+        assert torch.equal(fast, want)
+        assert torch.equal(acc, 2 * ref)
+        del acc, fast
+    xc.close()
