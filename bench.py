@@ -234,6 +234,34 @@ def path_kernels(torch, ops, dev, nchan, hbm_peak, iters=10):
     ab = ro.numel() * 4 + ro.numel() * 4 // 2     # every output word written, each stored word read once
     res["reorder"] = {"ms": ms, "alg_bytes": ab, "gbs": ab / ms / 1e6, "frac_hbm": ab / ms / 1e6 / hbm_peak}
     del ro, vis, acc
+    # fused Corr + CorrAcc + CorrSubsel step (configs[4]): one launch per gulp, 4704 baselines summed over 4 channels
+    ntime = 480
+    xc = ops.XCorr(nstand=NSTAND, npol=NPOL, nchan=nchan, ntime_gulp=ntime)
+    gulps = [torch.randint(0, 256, (ntime, nchan, NINPUT), dtype=torch.uint8, device=dev) for _ in range(4)]
+    acc2 = torch.zeros(nw, dtype=torch.int32, device=dev)
+    sel = np.random.default_rng(1).integers(0, a2bl.size, 4704)
+    xc.set_subsel(a2bl.reshape(-1)[sel].copy(), conj.reshape(-1)[sel].copy(), 4)
+    fast = torch.zeros((nchan // 4, 4704, 2), dtype=torch.int32, device=dev)
+    k = [0]
+
+    def fused():
+        xc.accumulate_subsel(gulps[k[0] % 4], acc2, False, fast)
+        k[0] += 1
+    def plain():
+        xc.accumulate(gulps[k[0] % 4], acc2, False)
+        k[0] += 1
+    ms_plain = timeit(plain, 20)
+    ms = timeit(fused, 20)
+    ab = ntime * nchan * NINPUT + 2 * 4 * nw + 8 * 4704 * nchan // 4
+    res["corr_acc_subsel_fused"] = {"ms": ms, "gsamples_per_s": ntime * nchan * NINPUT / ms / 1e6, "alg_bytes": ab,
+                                    "gbs": ab / ms / 1e6, "frac_hbm": ab / ms / 1e6 / hbm_peak,
+                                    "corr_acc_only_ms": ms_plain, "unfused_ms": None}
+    # the same work as the three separate blocks do it: Corr (writes the per-gulp matrix) + CorrAcc + CorrSubsel
+    ms_store = timeit(lambda: xc.run(gulps[0], acc2, True), 10)
+    res["corr_store"] = {"ms": ms_store, "gsamples_per_s": ntime * nchan * NINPUT / ms_store / 1e6}
+    res["corr_acc_subsel_fused"]["unfused_ms"] = ms_store + res["corr_acc"]["ms"] + res["corr_subsel_4704"]["ms"]
+    xc.close()
+    del gulps, acc2, fast
     nbeam, nt, nsum = 32, 960, 24
     bf = ops.Beamformer(ninput=NINPUT, nchan=nchan, ntime=nt, nbeam=nbeam)
     vv = torch.randint(0, 256, (nt, nchan, NINPUT), dtype=torch.uint8, device=dev)

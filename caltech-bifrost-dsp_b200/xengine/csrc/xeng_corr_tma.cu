@@ -155,6 +155,14 @@ __device__ __forceinline__ uint4 parity_hi(uint4 a, uint4 b) {
       for (int i__ = 0; i__ < 8; ++i__) a.trace[(role) * 8 + i__] = tacc[i__];             \
   } while (0)
 
+constexpr uint32_t SUB_NONE = 0xFFFFFFFFu;
+// one selected word: staging -> (negate the imaginary part where conj) -> out[v][plane] += value
+__device__ __forceinline__ void sub_emit(int32_t* so, uint32_t stg_w, uint32_t en, int plane) {
+  int val = static_cast<int>(lds_u32(stg_w + (en & 0x3FFFu)));
+  if (plane == 1 && ((en >> 14) & 1u)) val = -val;
+  asm volatile("red.global.add.s32 [%0], %1;" ::"l"(so + static_cast<long>(en >> 15) * 2), "r"(val) : "memory");
+}
+
 template <bool ABL, bool SUB>
 __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_constant__ CUtensorMap tmap, CorrArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -216,6 +224,14 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
     for (TileWalk tw(a); tw.valid(a); tw.next(a), ++it) {
       const Tile tl = tw.get();
       const int buf = it & 1;
+      int sub_lb = 0, sub_le = 0;
+      uint32_t sub_e0 = SUB_NONE, sub_e1 = SUB_NONE;
+      if (SUB) {     // this (tile, warp)'s selection list; its global-load latency hides behind the accumulator wait
+        sub_lb = a.sub_begin[tw.r * N_EPI_WARPS + warp];
+        sub_le = a.sub_begin[tw.r * N_EPI_WARPS + warp + 1];
+        if (sub_lb + lane < sub_le) sub_e0 = a.sub_entries[sub_lb + lane];
+        if (sub_lb + 32 + lane < sub_le) sub_e1 = a.sub_entries[sub_lb + 32 + lane];
+      }
       XTRACE(4, 0);
       mbar_wait(&S->tmem_full[buf], (it >> 1) & 1, a.err, 100 + buf);
       XTRACE(4, 1);
@@ -279,15 +295,12 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
         bulk_commit();
         if (SUB) {
           // fused CorrSubsel (corr_subsel_block.py:298): the selected words of this warp's 16 runs, straight from the
-          // staging buffer; the nchan_sum channels of one output row come from different tiles -> red.global.add
-          const int lb = a.sub_begin[tw.r * N_EPI_WARPS + warp], le = a.sub_begin[tw.r * N_EPI_WARPS + warp + 1];
+          // staging buffer; the nchan_sum channels of one output row come from different tiles -> red.global.add.
+          // The first 64 entries of the list were fetched before the accumulator wait (sub_e0 / sub_e1).
           int32_t* const so = a.sub_out + (static_cast<long>(tl.c / a.sub_nsum) * a.sub_nvis) * 2 + plane;
-          for (int e = lb + lane; e < le; e += 32) {
-            const uint32_t en = a.sub_entries[e];
-            int val = static_cast<int>(lds_u32(stg_w + (en & 0x3FFFu)));
-            if (plane == 1 && ((en >> 14) & 1u)) val = -val;          // imaginary part negated where conj[v]
-            atomicAdd(so + static_cast<long>(en >> 15) * 2, val);      // result unused -> RED.ADD
-          }
+          if (sub_e0 != SUB_NONE) sub_emit(so, stg_w, sub_e0, plane);
+          if (sub_e1 != SUB_NONE) sub_emit(so, stg_w, sub_e1, plane);
+          for (int e = sub_lb + 64 + lane; e < sub_le; e += 32) sub_emit(so, stg_w, a.sub_entries[e], plane);
         }
         XTRACE(4, 7);
       }
