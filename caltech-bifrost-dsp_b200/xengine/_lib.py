@@ -35,7 +35,7 @@ SIGNATURES = {
     "xeng_corr_run_host": (_i, [_vp, _vp, _vp, _i]),
     "xeng_corr_accumulate": (_i, [_vp, _vp, _vp, _i]),
     "xeng_corr_set_subsel": (_i, [_vp, _vp, _vp, _i, _i]),
-    "xeng_corr_accumulate_subsel": (_i, [_vp, _vp, _vp, _i, _vp]),
+    "xeng_corr_accumulate_subsel": (_i, [_vp, _vp, _vp, _i, _vp, _i]),
     "xeng_corr_sync": (_i, [_vp]),
     "xeng_get_order": (_i, [_vp, _vp, _vp, _i, _i]),
     "xeng_acc": (_i, [_vp, _vp, _sz, _i, _vp]),

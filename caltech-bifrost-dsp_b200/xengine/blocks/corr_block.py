@@ -12,7 +12,16 @@ Differences that do not change the data products:
     corr_block.py:421-435);
   * ``test=True`` cross-checks every dump on the GPU against the independent CUDA-core kernel instead of running
     numpy for ~10 minutes per gulp (corr_block.py:265-315).
+
+Optional fused fast-dump path (BASELINE configs[4]): three extra keyword arguments at the END of the signature,
+``fast_oring=None, nchan_sum=4, fast_nvis=4704``.  With ``fast_oring`` set, every integration is also written to that
+ring as CorrSubsel would write it (int32 [nchan/nchan_sum][nvis][2], CorrSubsel's header keys,
+corr_subsel_block.py:272-285) -- gathered inside the correlator kernel's epilogue (``xeng_corr_accumulate_subsel``), so
+no CorrSubsel block and no second pass over the 383 MB matrix are needed.  The selection is set with
+``update_fast_subsel(baselines)`` (same [[stand0, pol0], [stand1, pol1]] lists as CorrSubsel's ``baselines`` key) and
+takes effect at the next integration boundary.
 """
+import contextlib
 import json
 import time
 
@@ -41,7 +50,8 @@ def regtile_index(in0, in1, nstand):
 
 class Corr(Block):
     def __init__(self, log, iring, oring, ntime_gulp=2500, guarantee=True, core=-1, nchan=192, npol=2, nstand=352,
-                 acc_len=2400, gpu=-1, test=False, etcd_client=None, autostartat=0, ant_to_input=None):
+                 acc_len=2400, gpu=-1, test=False, etcd_client=None, autostartat=0, ant_to_input=None,
+                 fast_oring=None, nchan_sum=4, fast_nvis=4704):
         assert (acc_len % ntime_gulp == 0), "Acculmulation length must be a multiple of gulp size"
         super(Corr, self).__init__(log, iring, oring, guarantee, core, etcd_client=etcd_client)
         self.ntime_gulp, self.nchan, self.npol, self.nstand = ntime_gulp, nchan, npol, nstand
@@ -73,6 +83,40 @@ class Corr(Block):
         self.bl_is_conj = np.zeros([nstand, nstand, npol, npol], dtype=np.int32)
         if ant_to_input is not None:
             self.update_baseline_indices(ant_to_input)
+
+        # fused fast-dump path
+        self.fast_oring, self.nchan_sum, self.fast_nvis = fast_oring, nchan_sum, fast_nvis
+        self.fast_gulp_size = (nchan // nchan_sum) * fast_nvis * 8
+        self._fast_baselines = [[[i % nstand, 0], [i % nstand, 0]] for i in range(fast_nvis)]   # corr_subsel_block.py:230
+        self._fast_pending = fast_oring is not None
+
+    def update_fast_subsel(self, baselines):
+        """Selection of the fused fast dump: ``fast_nvis`` entries [[stand0, pol0], [stand1, pol1]]; loaded at the
+        next integration boundary (a new output sequence on the fast ring carries it in its header)."""
+        if len(baselines) != self.fast_nvis:
+            raise ValueError("expected %d baselines, got %d" % (self.fast_nvis, len(baselines)))
+        with self._control_lock:
+            self._fast_baselines = baselines
+            self._fast_pending = True
+
+    def _load_fast_selection(self):
+        with self._control_lock:
+            baselines = self._fast_baselines
+            self._fast_pending = False
+        bl = np.asarray(baselines, dtype=np.int64).reshape(self.fast_nvis, 2, 2)
+        s0, p0, s1, p1 = bl[:, 0, 0], bl[:, 0, 1], bl[:, 1, 0], bl[:, 1, 1]
+        self._xcorr.set_subsel(self.antpol_to_bl[s0, s1, p0, p1], self.bl_is_conj[s0, s1, p0, p1], self.nchan_sum)
+        return baselines
+
+    def _fast_header(self, ohdr, baselines):
+        """CorrSubsel's output header (corr_subsel_block.py:272-285) for the sequence described by ``ohdr``."""
+        fhdr = dict(ohdr)
+        fhdr['nchan'] = ohdr['nchan'] // self.nchan_sum
+        fhdr['nvis'] = self.fast_nvis
+        fhdr['sfreq'] = (ohdr['sfreq'] + (self.nchan_sum - 1) * (ohdr['bw_hz'] / ohdr['nchan'])) / self.nchan_sum
+        fhdr['baselines'] = baselines
+        fhdr['nchan_sum'] = self.nchan_sum
+        return fhdr
 
     def update_baseline_indices(self, ant_to_input):
         """Fill ``antpol_to_bl`` / ``bl_is_conj`` ([nstand, nstand, npol, npol]) from a [nstand, npol] map of
@@ -114,10 +158,16 @@ class Corr(Block):
         clock = IntegrationClock(recover_skip=10, asap="boundary")
         time_tag = 1
         self.update_stats({'state': 'starting'})
-        with self.oring.begin_writing() as oring:
+        with contextlib.ExitStack() as stack:
+            oring = stack.enter_context(self.oring.begin_writing())
+            foring = None
+            if self.fast_oring is not None:
+                self.fast_oring.resize(self.fast_gulp_size)
+                foring = stack.enter_context(self.fast_oring.begin_writing())
             prev = time.time()
             self.update_pending = True          # load the constructor's start_time / acc_len on the first gulp
             oseq = ospan = None
+            foseq = fspan = None
             for iseq in self.iring.read(guarantee=self.guarantee):
                 self.log.info('CORR >> new input sequence!')
                 ihdr = json.loads(iseq.header.tostring())
@@ -131,7 +181,7 @@ class Corr(Block):
                                   % (clock.start_time, clock.acc_len))
                     ohdr['acc_len'], ohdr['seq0'] = clock.acc_len, clock.start_time
                 self.sequence_proclog.update(ohdr)
-                ospan = None                    # an integration cut short by the end of a sequence is dropped
+                ospan = fspan = None            # an integration cut short by the end of a sequence is dropped
                 process_time = acquire_time = reserve_time = 0.
                 for ispan in iseq.read(self.igulp_size):
                     if ispan.size < self.igulp_size:
@@ -149,7 +199,9 @@ class Corr(Block):
                         self.update_stats({'state': 'stopped'})
                         if oseq:
                             oseq.end()
-                        oseq = ospan = None
+                        if foseq:
+                            foseq.end()
+                        oseq = ospan = foseq = fspan = None
                         clock.stop()
                         now += step
                         continue
@@ -160,6 +212,12 @@ class Corr(Block):
                         self.sequence_proclog.update(ohdr)
                         oseq = oring.begin_sequence(time_tag=time_tag, header=json.dumps(ohdr),
                                                     nringlet=iseq.nringlet)
+                        if foring is not None:
+                            if foseq:
+                                foseq.end()
+                            fhdr = self._fast_header(ohdr, self._load_fast_selection())
+                            foseq = foring.begin_sequence(time_tag=time_tag, header=json.dumps(fhdr),
+                                                          nringlet=iseq.nringlet)
                         time_tag += 1
                     if not clock.running:
                         self.update_stats({'state': 'waiting'})
@@ -171,6 +229,15 @@ class Corr(Block):
                     is_first, is_last = (now == clock.first), (now == clock.last)
                     if is_first:
                         ospan = rt.WriteSpan(oseq.ring, self.ogulp_size, nonblocking=False)
+                        if foring is not None:
+                            if self._fast_pending:      # new selection: new fast sequence with an updated header
+                                foseq.end()
+                                fhdr = self._fast_header(ohdr, self._load_fast_selection())
+                                fhdr['seq0'] = now
+                                foseq = foring.begin_sequence(time_tag=time_tag, header=json.dumps(fhdr),
+                                                              nringlet=iseq.nringlet)
+                                time_tag += 1
+                            fspan = rt.WriteSpan(foseq.ring, self.fast_gulp_size, nonblocking=False)
                         t = time.time()
                         reserve_time, prev = t - prev, t
                     if ospan is None:
@@ -178,7 +245,10 @@ class Corr(Block):
                         now += step
                         continue
                     # device boundary (replaces _bf.bfXgpuKernel, corr_block.py:445): ospan (+)= X(ispan)
-                    self._xcorr.accumulate(ispan.data, ospan.data, is_first)
+                    if fspan is not None:       # the same launch also gathers the fast-dump selection
+                        self._xcorr.accumulate_subsel(ispan.data, ospan.data, is_first, fspan.data, is_first)
+                    else:
+                        self._xcorr.accumulate(ispan.data, ospan.data, is_first)
                     if self.test:
                         self._crosscheck_gulp(ispan.data, is_first)
                     self._xcorr.sync()          # the input span may be released when this iteration ends
@@ -190,6 +260,9 @@ class Corr(Block):
                             self._crosscheck_compare(ospan.data)
                         ospan.close()
                         ospan = None
+                        if fspan is not None:
+                            fspan.close()
+                            fspan = None
                         gbps = 8 * clock.acc_len * ihdr['nchan'] * ihdr['nstand'] * ihdr['npol'] / process_time / 1e9
                         self.perf_proclog.update({'acquire_time': acquire_time, 'reserve_time': reserve_time,
                                                   'process_time': process_time, 'gbps': gbps})
@@ -199,4 +272,6 @@ class Corr(Block):
                     now += step
                 if oseq:
                     oseq.end()
-                oseq = None
+                if foseq:
+                    foseq.end()
+                oseq = foseq = None

@@ -292,14 +292,16 @@ int xeng_corr_set_subsel(xeng_corr_t h, const int32_t* vismap, const int32_t* co
   return XENG_OK;
 }
 
-int xeng_corr_accumulate_subsel(xeng_corr_t h, const void* d_in, void* d_acc, int first, void* d_sub_out) {
+int xeng_corr_accumulate_subsel(xeng_corr_t h, const void* d_in, void* d_acc, int first, void* d_sub_out,
+                                int sub_first) {
   int rc = corr_check(h, d_in, d_acc, true);
   if (rc) return rc;
   if (!d_sub_out) return fail(XENG_ERR_ARG, "null sub-select output pointer");
   if (h->sub_nvis <= 0) return fail(XENG_ERR_ARG, "no selection set: call xeng_corr_set_subsel first");
   int32_t* so = static_cast<int32_t*>(d_sub_out);
   if (corr_uses_tma(h, d_in, d_acc)) {   // one launch: correlate, accumulate in L2, sub-select from the staging buffers
-    XENG_CUDA(cudaMemsetAsync(so, 0, sizeof(int32_t) * 2 * h->sub_nvis * (h->nchan / h->sub_nsum), h->stream));
+    if (sub_first)
+      XENG_CUDA(cudaMemsetAsync(so, 0, sizeof(int32_t) * 2 * h->sub_nvis * (h->nchan / h->sub_nsum), h->stream));
     return corr_launch(h, d_in, static_cast<int32_t*>(d_acc), first ? 0 : 1, so);
   }
   // shapes the TMA kernel cannot take: per-gulp visibilities into a scratch buffer, then the stand-alone kernels
@@ -308,8 +310,18 @@ int xeng_corr_accumulate_subsel(xeng_corr_t h, const void* d_in, void* d_acc, in
   rc = corr_launch(h, d_in, h->d_sub_scratch, 0);
   if (rc) return rc;
   XENG_CUDA(xeng::launch_acc(static_cast<int32_t*>(d_acc), h->d_sub_scratch, words, first ? 1 : 0, h->stream));
-  XENG_CUDA(xeng::launch_subsel(h->d_sub_scratch, so, h->d_sub_vismap, h->d_sub_conj, h->sub_nvis, h->nchan,
-                                h->sub_nsum, h->words_per_chan, h->stream));
+  if (sub_first) {
+    XENG_CUDA(xeng::launch_subsel(h->d_sub_scratch, so, h->d_sub_vismap, h->d_sub_conj, h->sub_nvis, h->nchan,
+                                  h->sub_nsum, h->words_per_chan, h->stream));
+  } else {      // sub_out += sel(X): select into the (now free) head of the scratch buffer, then add
+    const size_t nsel = static_cast<size_t>(2) * h->sub_nvis * (h->nchan / h->sub_nsum);
+    int32_t* tmp = nullptr;
+    XENG_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&tmp), nsel * sizeof(int32_t), h->stream));
+    XENG_CUDA(xeng::launch_subsel(h->d_sub_scratch, tmp, h->d_sub_vismap, h->d_sub_conj, h->sub_nvis, h->nchan,
+                                  h->sub_nsum, h->words_per_chan, h->stream));
+    XENG_CUDA(xeng::launch_acc(so, tmp, nsel, 0, h->stream));
+    XENG_CUDA(cudaFreeAsync(tmp, h->stream));
+  }
   return XENG_OK;
 }
 

@@ -57,11 +57,11 @@ class XCorr(object):
               "xeng_corr_set_subsel")
         self.nvis, self.nchan_sum = int(vm.size), int(nchan_sum)
 
-    def accumulate_subsel(self, d_in, d_acc, first, d_sub_out):
-        """Fused Corr + CorrAcc + CorrSubsel step: d_acc (=|+=) X(d_in); d_sub_out[nchan/nchan_sum][nvis][2] = this
+    def accumulate_subsel(self, d_in, d_acc, first, d_sub_out, sub_first=True):
+        """Fused Corr + CorrAcc + CorrSubsel step: d_acc (=|+=) X(d_in); d_sub_out[nchan/nchan_sum][nvis][2] (=|+=) this
         gulp's selected visibilities summed over nchan_sum channels."""
-        check(self._lib.xeng_corr_accumulate_subsel(self._h, ptr(d_in), ptr(d_acc), int(bool(first)), ptr(d_sub_out)),
-              "xeng_corr_accumulate_subsel")
+        check(self._lib.xeng_corr_accumulate_subsel(self._h, ptr(d_in), ptr(d_acc), int(bool(first)), ptr(d_sub_out),
+                                                    int(bool(sub_first))), "xeng_corr_accumulate_subsel")
 
     def sync(self):
         check(self._lib.xeng_corr_sync(self._h), "xeng_corr_sync")

@@ -65,12 +65,14 @@ int xeng_corr_accumulate(xeng_corr_t h, const void* d_in, void* d_acc, int first
  * corr_subsel_block.py:298 in ONE launch).  xeng_corr_set_subsel takes the HOST arrays CorrSubsel.update_subsel
  * builds (corr_subsel_block.py:237-250): vismap[v] = word index inside one channel of the xGPU buffer, conj[v] != 0
  * where the imaginary part is negated; nvis = 0 clears the selection.  xeng_corr_accumulate_subsel then does
- * d_acc (=|+=) X(d_in) as xeng_corr_accumulate and writes this gulp's selection, summed over nchan_sum adjacent
- * channels, to d_sub_out: device int32 [nchan/nchan_sum][nvis][2] (re, im) -- the bfXgpuSubSelect output layout.
+ * d_acc (=|+=) X(d_in) as xeng_corr_accumulate and puts this gulp's selection, summed over nchan_sum adjacent
+ * channels, into d_sub_out: device int32 [nchan/nchan_sum][nvis][2] (re, im) -- the bfXgpuSubSelect output layout;
+ * sub_first != 0: d_sub_out = sel(X), else d_sub_out += sel(X) (a fast dump that spans several gulps).
  * The selected words are taken from the epilogue's staging buffers (no per-gulp visibility matrix is written);
  * shapes the TMA kernel cannot take run Corr -> scratch, xeng_acc, xeng_subsel instead. */
 int xeng_corr_set_subsel(xeng_corr_t h, const int32_t* vismap, const int32_t* conj, int nvis, int nchan_sum);
-int xeng_corr_accumulate_subsel(xeng_corr_t h, const void* d_in, void* d_acc, int first, void* d_sub_out);
+int xeng_corr_accumulate_subsel(xeng_corr_t h, const void* d_in, void* d_acc, int first, void* d_sub_out,
+                                int sub_first);
 int xeng_corr_sync(xeng_corr_t h);
 
 /* Replaces bfXgpuGetOrder(antpol_to_input, antpol_to_bl, bl_is_conj) -- corr_block.py:331-333.  HOST arrays.

@@ -141,6 +141,50 @@ def test_correlator_graph_matches_oracle(torch_cuda):
         assert np.array_equal(sp.view(np.int32).reshape(want.shape), want.astype(np.int32)), "slow dump %d" % k
 
 
+def test_correlator_graph_fused_fast_dump(torch_cuda):
+    """BASELINE configs[4] at block level: Corr(fast_oring=...) emits what Corr -> CorrSubsel emits (same header keys,
+    same bytes) from the single fused launch, alongside the unchanged slow path through CorrAcc."""
+    from xengine import ringshim
+    from xengine.blocks import Corr, CorrAcc
+    nstand, npol, nchan, nt, nvis = 32, 2, 8, 32, 4704
+    corr_acc_len, long_acc_len, ngulp = 2 * nt, 4 * nt, 13
+    rng = np.random.default_rng(0xfeed)
+    v = rng.integers(0, 256, size=(ngulp, nt, nchan, nstand, npol), dtype=np.uint8)
+    r_in = ringshim.Ring("gpu-input", space="cuda")
+    r_corr = ringshim.Ring("corr-output", space="cuda")
+    r_slow = ringshim.Ring("corr-slow-output", space="cuda_host")
+    r_fast = ringshim.Ring("corr-fast-output", space="cuda")
+    hdr = header(nchan, nstand, npol)
+    corr = Corr(LOG, r_in, r_corr, ntime_gulp=nt, nchan=nchan, npol=npol, nstand=nstand, acc_len=corr_acc_len,
+                gpu=0, autostartat=nt, ant_to_input=np.array(hdr['ant_to_input']), fast_oring=r_fast, nchan_sum=4,
+                fast_nvis=nvis)
+    acc = CorrAcc(LOG, r_corr, r_slow, nchan=nchan, npol=npol, nstand=nstand, acc_len=long_acc_len, gpu=0,
+                  autostartat=nt + corr_acc_len)
+    bls = [[[int(a), int(b)], [int(c), int(d)]] for a, b, c, d in
+           zip(rng.integers(0, nstand, nvis), rng.integers(0, 2, nvis), rng.integers(0, nstand, nvis),
+               rng.integers(0, 2, nvis))]
+    corr.update_fast_subsel(bls)
+    slow, fast = [], []
+    run_all([source(r_in, hdr, list(v)), threading.Thread(target=corr.main, name="Corr"),
+             threading.Thread(target=acc.main, name="CorrAcc"),
+             sink(r_slow, acc.ogulp_size, slow), sink(r_fast, corr.fast_gulp_size, fast)])
+    want_corr = [orc.corr_xgpu(v[1 + 2 * k]) + orc.corr_xgpu(v[2 + 2 * k]) for k in range(6)]
+    (fh, fspans), = fast
+    assert fh['nchan'] == nchan // 4 and fh['nvis'] == nvis and fh['nchan_sum'] == 4 and fh['baselines'] == bls
+    assert fh['seq0'] == nt and fh['acc_len'] == corr_acc_len
+    assert fh['sfreq'] == (hdr['sfreq'] + 3 * hdr['bw_hz'] / nchan) / 4
+    vm, cj = orc.baselines_to_vismap(bls, corr.antpol_to_bl, corr.bl_is_conj)
+    assert len(fspans) == 6
+    for k, sp in enumerate(fspans):
+        got = sp.view(np.int32).reshape(nchan // 4, nvis, 2)
+        assert np.array_equal(got, orc.subselect(want_corr[k].astype(np.int32), vm, cj, 4)), "fused fast dump %d" % k
+    (sh, sspans), = slow
+    assert len(sspans) == 2
+    for k, sp in enumerate(sspans):
+        want = want_corr[1 + 2 * k] + want_corr[2 + 2 * k]
+        assert np.array_equal(sp.view(np.int32).reshape(want.shape), want.astype(np.int32)), "slow dump %d" % k
+
+
 def test_beamformer_graph_matches_oracle(torch_cuda):
     from xengine import ringshim
     from xengine.blocks import Beamform, BeamformSumBeams
