@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libxeng.so")
+LIB_PATH = os.environ.get("XENG_LIB_PATH") or os.path.join(_HERE, "libxeng.so")   # override: developer timing builds
 
 XENG_OK = 0
 

@@ -29,11 +29,15 @@
 // needs >= 4 MMAs per barrier round trip to keep the tensor pipe fed; the bulk-reduce path itself sustains
 // 3.17 TB/s of payload (= HBM read + write), i.e. the HBM roofline.
 //
-// Roles (576 threads): warps 0-7 epilogue, 8-11 unpack group 0, 12-15 unpack group 1, 16 TMA producer, 17 MMA issuer.
+// Roles (832 threads): warps 0-7 epilogue, 8-15 unpack group 0, 16-23 unpack group 1, 24 TMA producer, 25 MMA issuer.
 #include <cuda.h>
 
 #include "xeng_ptx.cuh"
 #include "xeng_internal.h"
+
+#ifndef XENG_CT_ABLATE
+#define XENG_CT_ABLATE 0
+#endif
 
 namespace xeng {
 namespace {
@@ -55,7 +59,7 @@ constexpr int RUN_BYTES = PAIRS * 16;                      // 32 cells x 4 words
 constexpr int RUN_STRIDE = RUN_BYTES + 16;
 constexpr int HALF_SKEW = 64;                              // quadrant half b1 = 1 starts 64 B later (bank skew)
 constexpr int WARP_STAGING = 16 * RUN_STRIDE + HALF_SKEW + 64;   // 8576: the 16 runs one epilogue warp stages
-constexpr int N_EPI_WARPS = 8, N_GROUP_WARPS = 4, N_GROUPS = 2;
+constexpr int N_EPI_WARPS = 8, N_GROUP_WARPS = 4 * KB, N_GROUPS = 2;   // a group = 4 warps per 32-sample K-block
 constexpr int WARP_TMA = N_EPI_WARPS + N_GROUPS * N_GROUP_WARPS, WARP_MMA = WARP_TMA + 1;
 constexpr int N_THREADS = (WARP_MMA + 1) * 32;
 constexpr int N_GROUP = N_GROUP_WARPS * 32;                // threads per unpack group
@@ -70,8 +74,8 @@ struct SmemHdr {
   uint64_t tmem_empty[2];
   uint32_t tmem_base;
 };
-constexpr int SMEM_HDR = 2048;                             // barriers + 1 KB scratch; raw panels stay 1024-byte aligned
-constexpr int SCRATCH_OFF = 1024;                          // one dummy word per unpack thread (mbar_arrive_after)
+constexpr int SMEM_HDR = 4096;                             // barriers + 2 KB scratch; raw panels stay 1024-byte aligned
+constexpr int SCRATCH_OFF = 2048;                          // one dummy word per unpack thread (mbar_arrive_after)
 static_assert(sizeof(SmemHdr) <= SMEM_HDR, "header");
 static_assert(STAGE_BYTES % 128 == 0 && WARP_STAGING % 128 == 0, "alignment");
 constexpr int SMEM_BYTES = SMEM_HDR + RAW_STAGES * RAW_STAGE_BYTES + NSTAGE * STAGE_BYTES + N_EPI_WARPS * WARP_STAGING + 1024;
@@ -178,7 +182,7 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
   const int warp = static_cast<int>(__reduce_min_sync(0xffffffffu, threadIdx.x >> 5));
   const int lane = threadIdx.x & 31;
   const int n_kstage = (a.ntime + ST_T - 1) / ST_T;     // the TMA zero-fills samples past ntime
-  const int ablate = ABL ? a.ablate : 0;
+  const int ablate = ABL ? a.ablate : XENG_CT_ABLATE;   // XENG_CT_ABLATE: compile-time ablation of developer timing builds
   uint32_t tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   uint32_t tlast = static_cast<uint32_t>(clock64());
   (void)tacc; (void)tlast;
@@ -310,11 +314,12 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
   } else if (warp < WARP_TMA) {
     // ===================================================================== unpack: raw ring -> operand planes
     const int grp = (warp - N_EPI_WARPS) / N_GROUP_WARPS;          // stages with (index & 1) == grp
-    const int wg = (warp - N_EPI_WARPS) % N_GROUP_WARPS;
-    const int tlow = lane & 7, c = lane >> 3;                        // sample wg*8 + tlow, inputs 32c .. 32c+31
+    const int kb = ((warp - N_EPI_WARPS) % N_GROUP_WARPS) >> 2;     // the 32-sample K-block of the stage this warp unpacks
+    const int wg = (warp - N_EPI_WARPS) & 3;
+    const int tlow = lane & 7, c = lane >> 3;                        // sample 32*kb + wg*8 + tlow, inputs 32c .. 32c+31
     // swizzled raw row: logical 16-byte chunk j of row t sits at chunk j ^ (t & 7)
-    const uint32_t lds_a = (wg * 8 + tlow) * TILE + (((2 * c) ^ tlow) << 4), lds_b = lds_a ^ 16u;
-    const uint32_t kofs = wg * KGRP_BYTES + tlow * 16;               // K position inside a 16-input group
+    const uint32_t lds_a = (kb * 32 + wg * 8 + tlow) * TILE + (((2 * c) ^ tlow) << 4), lds_b = lds_a ^ 16u;
+    const uint32_t kofs = (kb * 4 + wg) * KGRP_BYTES + tlow * 16;    // K position inside a 16-input group
     const uint32_t stsA = (2 * c) * SBO + kofs;                      // tile rows 32c .. 32c+15, next group +SBO
     const uint32_t stsB = c * SBO + kofs;                            // columns n = 16c .. (b0 = 0), +4*SBO for b0 = 1
     const uint32_t raw0 = smem_u32(raw), stages0 = smem_u32(stages);
@@ -330,58 +335,48 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
         mbar_wait(&S->raw_full[rs], (gs / RAW_STAGES) & 1, a.err, 500 + rs);
         XTRACE(grp, 1);
         const uint32_t rbase = raw0 + rs * RAW_STAGE_BYTES;
-        const int nkb = min(KB, (a.ntime - ks * ST_T + 31) >> 5);      // K-blocks of this stage that hold samples
-        uint4 rawA[KB][2], rawB[KB][2];
-#pragma unroll
-        for (int j = 0; j < KB; ++j) {
-          if (j < nkb) {
-            rawA[j][0] = lds_v4(rbase + j * (32 * TILE) + lds_a);
-            rawA[j][1] = lds_v4(rbase + j * (32 * TILE) + lds_b);
-            rawB[j][0] = lds_v4(rbase + boff + j * (32 * TILE) + lds_a);
-            rawB[j][1] = lds_v4(rbase + boff + j * (32 * TILE) + lds_b);
+        const bool live = kb * 32 < a.ntime - ks * ST_T;               // this K-block holds samples (else: not issued)
+        uint4 rawA0, rawA1, rawB0, rawB1;
+        rawA0 = rawA1 = rawB0 = rawB1 = make_uint4(0u, 0u, 0u, 0u);
+        if (live) {
+          rawA0 = lds_v4(rbase + lds_a);
+          rawA1 = lds_v4(rbase + lds_b);
+          rawB0 = lds_v4(rbase + boff + lds_a);
+          rawB1 = lds_v4(rbase + boff + lds_b);
+        }
+        // The TMA warp may refill the raw slot once the loads have RETURNED, not merely issued (SYNCS.ARRIVE does
+        // not wait for outstanding LDS): make the arrive depend on one word of every load.
+        mbar_arrive_after(&S->raw_empty[rs], scratch, rawA0.x ^ rawA1.x ^ rawB0.x ^ rawB1.x);
+        const uint32_t base = stages0 + slot * STAGE_BYTES;
+        uint4 reA0, imA0, reA1, imA1, reB0, imB0, reB1, imB1, nimB0, nimB1;
+        if (live) {
+          const uint4 colB0 = parity_lo(rawB0, rawB1), colB1 = parity_hi(rawB0, rawB1);
+          if (ABL && (ablate & 16)) {
+            reA0 = imA0 = rawA0; reA1 = imA1 = rawA1;
+            reB0 = imB0 = nimB0 = colB0; reB1 = imB1 = nimB1 = colB1;
+          } else {
+            reA0 = re16(rawA0); imA0 = im16(rawA0); reA1 = re16(rawA1); imA1 = im16(rawA1);
+            reB0 = re16(colB0); imB0 = im16(colB0); reB1 = re16(colB1); imB1 = im16(colB1);
+            nimB0 = neg16(imB0); nimB1 = neg16(imB1);
           }
         }
-        {
-          // The TMA warp may refill the raw slot once the loads have RETURNED, not merely issued (SYNCS.ARRIVE does
-          // not wait for outstanding LDS): make the arrive depend on one word of every load.
-          uint32_t dep = 0;
-#pragma unroll
-          for (int j = 0; j < KB; ++j)
-            if (j < nkb) dep ^= rawA[j][0].x ^ rawA[j][1].x ^ rawB[j][0].x ^ rawB[j][1].x;
-          mbar_arrive_after(&S->raw_empty[rs], scratch, dep);
-        }
-        const uint32_t base = stages0 + slot * STAGE_BYTES;
-#pragma unroll
-        for (int j = 0; j < KB; ++j) {
-          if (j < nkb) {
-            const uint4 colB0 = parity_lo(rawB[j][0], rawB[j][1]), colB1 = parity_hi(rawB[j][0], rawB[j][1]);
-            uint4 reA0, imA0, reA1, imA1, reB0, imB0, reB1, imB1, nimB0, nimB1;
-            if (ABL && (ablate & 16)) {
-              reA0 = imA0 = rawA[j][0]; reA1 = imA1 = rawA[j][1];
-              reB0 = imB0 = nimB0 = colB0; reB1 = imB1 = nimB1 = colB1;
-            } else {
-              reA0 = re16(rawA[j][0]); imA0 = im16(rawA[j][0]); reA1 = re16(rawA[j][1]); imA1 = im16(rawA[j][1]);
-              reB0 = re16(colB0); imB0 = im16(colB0); reB1 = re16(colB1); imB1 = im16(colB1);
-              nimB0 = neg16(imB0); nimB1 = neg16(imB1);
-            }
-            if (j == 0) {
-              XTRACE(grp, 2);
-              mbar_wait(&S->empty[slot], ((gs / NSTAGE) & 1) ^ 1, a.err, 200 + slot);
-              XTRACE(grp, 3);
-            }
-            if (!(ablate & 8)) {
-              const uint32_t bj = base + j * (4 * KGRP_BYTES);
-              sts_v4(bj + OFF_A_RE + stsA, reA0);
-              sts_v4(bj + OFF_A_RE + stsA + SBO, reA1);
-              sts_v4(bj + OFF_A_IM + stsA, imA0);
-              sts_v4(bj + OFF_A_IM + stsA + SBO, imA1);
-              sts_v4(bj + OFF_B_IM + stsB, imB0);
-              sts_v4(bj + OFF_B_IM + stsB + 4 * SBO, imB1);
-              sts_v4(bj + OFF_B_RE + stsB, reB0);
-              sts_v4(bj + OFF_B_RE + stsB + 4 * SBO, reB1);
-              sts_v4(bj + OFF_B_NIM + stsB, nimB0);
-              sts_v4(bj + OFF_B_NIM + stsB + 4 * SBO, nimB1);
-            }
+        // every thread waits, live or not: a parity wait that is skipped leaves the thread a phase behind, and its next
+        // wait on this barrier would then be satisfied one MMA too early
+        XTRACE(grp, 2);
+        mbar_wait(&S->empty[slot], ((gs / NSTAGE) & 1) ^ 1, a.err, 200 + slot);
+        XTRACE(grp, 3);
+        if (live) {
+          if (!(ablate & 8)) {
+            sts_v4(base + OFF_A_RE + stsA, reA0);
+            sts_v4(base + OFF_A_RE + stsA + SBO, reA1);
+            sts_v4(base + OFF_A_IM + stsA, imA0);
+            sts_v4(base + OFF_A_IM + stsA + SBO, imA1);
+            sts_v4(base + OFF_B_IM + stsB, imB0);
+            sts_v4(base + OFF_B_IM + stsB + 4 * SBO, imB1);
+            sts_v4(base + OFF_B_RE + stsB, reB0);
+            sts_v4(base + OFF_B_RE + stsB + 4 * SBO, reB1);
+            sts_v4(base + OFF_B_NIM + stsB, nimB0);
+            sts_v4(base + OFF_B_NIM + stsB + 4 * SBO, nimB1);
           }
         }
         XTRACE(grp, 4);
@@ -390,7 +385,7 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
         mbar_arrive(&S->full[slot]);
       }
     }
-    if (wg == 0 && lane == 0) XTRACE_DUMP(grp);
+    if (kb == 0 && wg == 0 && lane == 0) XTRACE_DUMP(grp);
   } else if (warp == WARP_TMA) {
     // ===================================================================== TMA producer (one lane)
     if (lane == 0) {
