@@ -233,7 +233,12 @@ def path_kernels(torch, ops, dev, nchan, hbm_peak, iters=10):
     ms = timeit(lambda: ops.reorder(vis, ro, da, dc, NSTAND, NPOL, nchan, wpc), 4)
     ab = ro.numel() * 4 + ro.numel() * 4 // 2     # every output word written, each stored word read once
     res["reorder"] = {"ms": ms, "alg_bytes": ab, "gbs": ab / ms / 1e6, "frac_hbm": ab / ms / 1e6 / hbm_peak}
-    del ro, vis, acc
+    nbl = NSTAND * (NSTAND + 1) // 2
+    pk = torch.zeros((nbl, nchan, 2, 2, 2), dtype=torch.int32, device=dev)
+    ms = timeit(lambda: ops.reorder_packets(vis, pk, da, dc, NSTAND, NPOL, nchan, wpc, ops.PAYLOAD_COR), 4)
+    ab = pk.numel() * 4 * 2                       # each valid word read once, written once
+    res["reorder_cor_payloads"] = {"ms": ms, "alg_bytes": ab, "gbs": ab / ms / 1e6, "frac_hbm": ab / ms / 1e6 / hbm_peak}
+    del ro, pk, vis, acc
     # fused Corr + CorrAcc + CorrSubsel step (configs[4]): one launch per gulp, 4704 baselines summed over 4 channels
     ntime = 480
     xc = ops.XCorr(nstand=NSTAND, npol=NPOL, nchan=nchan, ntime_gulp=ntime)

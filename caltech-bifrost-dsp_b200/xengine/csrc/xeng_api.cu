@@ -397,7 +397,20 @@ int xeng_reorder(const void* d_in, void* d_out, const void* d_a2bl, const void* 
   if (nstand <= 0 || npol <= 0 || nchan <= 0) return fail(XENG_ERR_ARG, "bad sizes");
   XENG_CUDA(xeng::launch_reorder(static_cast<const int32_t*>(d_in), static_cast<int32_t*>(d_out),
                                  static_cast<const int32_t*>(d_a2bl), static_cast<const int32_t*>(d_conj), nstand,
-                                 npol, nchan, words_per_chan, static_cast<cudaStream_t>(stream)));
+                                 npol, nchan, words_per_chan, 0, static_cast<cudaStream_t>(stream)));
+  return XENG_OK;
+}
+
+int xeng_reorder_packets(const void* d_in, void* d_out, const void* d_a2bl, const void* d_conj, int nstand, int npol,
+                         int nchan, int64_t words_per_chan, int layout, void* stream) {
+  if (!d_in || !d_out || !d_a2bl || !d_conj) return fail(XENG_ERR_ARG, "null pointer");
+  if (nstand <= 0 || nchan <= 0) return fail(XENG_ERR_ARG, "bad sizes");
+  if (npol != 2) return fail(XENG_ERR_ARG, "packet payload layouts are dual-pol only");
+  if (layout != XENG_PAYLOAD_COR && layout != XENG_PAYLOAD_PY) return fail(XENG_ERR_ARG, "unknown payload layout");
+  if (reinterpret_cast<uintptr_t>(d_out) & 15) return fail(XENG_ERR_ARG, "d_out must be 16-byte aligned");
+  XENG_CUDA(xeng::launch_reorder(static_cast<const int32_t*>(d_in), static_cast<int32_t*>(d_out),
+                                 static_cast<const int32_t*>(d_a2bl), static_cast<const int32_t*>(d_conj), nstand,
+                                 npol, nchan, words_per_chan, layout, static_cast<cudaStream_t>(stream)));
   return XENG_OK;
 }
 

@@ -95,6 +95,96 @@ __global__ void __launch_bounds__(1024) reorder_kernel(const int32_t* __restrict
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Tiled reorder for npol == 2.  One block = one second stand s1, 32 first stands s0 of one parity
+// (s0 = par + 2 (32 jc + k) <= s1) and 32 channels.  With the usual antenna map those 32 baselines are 32
+// neighbouring 16-byte cells of one xGPU register-tile row, so the gathers of a warp cover whole sectors; the
+// tile is turned through shared memory so that the writes run along channel.  Still table-driven (a2bl / conj),
+// so any antenna map gives the same answer.
+//   RO_FULL: out[s0][s1][p0][p1][chan][2] and the mirrored entry [s1][s0][...] (bfXgpuReorder,
+//            corr_output_full_block.py:669, shape :392)
+//   RO_COR : out[bl][chan][p0][p1][2], bl = upper-triangle baseline number, s0-major -- the "COR" packet
+//            payload send_packets_bf() builds with transpose([0,3,1,2,4]) (corr_output_full_block.py:505-511)
+//   RO_PY  : out[bl][p0][p1][chan][2] -- the payload of send_packets_py() (corr_output_full_block.py:457-460)
+enum { RO_FULL = 0, RO_COR = 1, RO_PY = 2 };
+constexpr int RO_ROW = 4 * 32 + 1;   // int2 per k row: 4 pol products x 32 channels, +1 keeps STS.64 conflict-free
+
+template <int MODE>
+__global__ void __launch_bounds__(1024) reorder_tile_kernel(const int32_t* __restrict__ in, int2* __restrict__ out,
+                                                            const int32_t* __restrict__ a2bl,
+                                                            const int32_t* __restrict__ conj, int nstand, int nchan,
+                                                            long W, long plane_words, int nchunk) {
+  __shared__ int2 tile[32 * RO_ROW];
+  __shared__ int tab[32 * 4];                              // word index | conj << 31 of the block's 32 x 4 entries
+  // blockIdx.x walks the (parity, chunk) groups; group g = 2 jc + par holds the second stands s1 >= its first s0
+  int s0_first = 0, s1 = blockIdx.x;
+  for (int g = 0; g < 2 * nchunk; ++g) {
+    s0_first = (g & 1) + 64 * (g >> 1);
+    const int n = nstand - s0_first;
+    if (s1 < n) break;
+    s1 -= n;
+  }
+  s1 += s0_first;
+  const int c0 = blockIdx.y * 32;
+#pragma unroll 1
+  for (int mirror = 0; mirror < (MODE == RO_FULL ? 2 : 1); ++mirror) {
+    if (mirror) __syncthreads();
+    if (threadIdx.y < 4) {  // table entries once per block, not once per channel
+      const int s0 = s0_first + 2 * threadIdx.x;
+      if (s0 <= s1) {
+        const long e = ((mirror ? static_cast<long>(s1) * nstand + s0 : static_cast<long>(s0) * nstand + s1)) * 4 +
+                       threadIdx.y;
+        tab[threadIdx.x * 4 + threadIdx.y] = __ldg(a2bl + e) | (__ldg(conj + e) ? 0x80000000 : 0);
+      }
+    }
+    __syncthreads();
+    {  // gather: lanes along the 32 first stands, warps along channel
+      const int s0 = s0_first + 2 * threadIdx.x;
+      const int c = c0 + threadIdx.y;
+      if (s0 <= s1 && c < nchan) {
+        const int32_t* pre = in + static_cast<long>(c) * W;
+        const int32_t* pim = pre + plane_words;
+        const int4 t4 = *reinterpret_cast<const int4*>(tab + threadIdx.x * 4);
+        const int tt[4] = {t4.x, t4.y, t4.z, t4.w};
+        int re[4], im[4];
+#pragma unroll
+        for (int pp = 0; pp < 4; ++pp) {
+          re[pp] = __ldg(pre + (tt[pp] & 0x7fffffff));
+          im[pp] = __ldg(pim + (tt[pp] & 0x7fffffff));
+        }
+#pragma unroll
+        for (int pp = 0; pp < 4; ++pp)
+          tile[threadIdx.x * RO_ROW + pp * 32 + threadIdx.y] = make_int2(re[pp], tt[pp] < 0 ? -im[pp] : im[pp]);
+      }
+    }
+    __syncthreads();
+    {  // scatter: lanes along channel, warps along the 32 first stands
+      const int s0 = s0_first + 2 * threadIdx.y;
+      const int c = c0 + threadIdx.x;
+      if (s0 <= s1 && c < nchan && !(mirror && s0 == s1)) {
+        const int2* t = tile + threadIdx.y * RO_ROW + threadIdx.x;
+        if (MODE == RO_FULL) {
+          const long e = ((mirror ? static_cast<long>(s1) * nstand + s0 : static_cast<long>(s0) * nstand + s1)) * 4;
+#pragma unroll
+          for (int pp = 0; pp < 4; ++pp) out[(e + pp) * nchan + c] = t[pp * 32];
+        } else {
+          const long bl = static_cast<long>(s0) * nstand - (static_cast<long>(s0) * (s0 - 1)) / 2 + (s1 - s0);
+          if (MODE == RO_PY) {
+#pragma unroll
+            for (int pp = 0; pp < 4; ++pp) out[(bl * 4 + pp) * nchan + c] = t[pp * 32];
+          } else {
+            int4* o = reinterpret_cast<int4*>(out + (bl * nchan + c) * 4);
+            const int2 v0 = t[0], v1 = t[32], v2 = t[64], v3 = t[96];
+            o[0] = make_int4(v0.x, v0.y, v1.x, v1.y);
+            o[1] = make_int4(v2.x, v2.y, v3.x, v3.y);
+          }
+        }
+      }
+    }
+  }
+}
+
 }  // namespace
 
 cudaError_t launch_acc(int32_t* acc, const int32_t* in, size_t n, int first, cudaStream_t stream) {
@@ -128,12 +218,31 @@ cudaError_t launch_subsel(const int32_t* in, int32_t* out, const int32_t* vismap
 }
 
 cudaError_t launch_reorder(const int32_t* in, int32_t* out, const int32_t* a2bl, const int32_t* conj, int nstand,
-                           int npol, int nchan, long W, cudaStream_t stream) {
+                           int npol, int nchan, long W, int layout, cudaStream_t stream) {
   const long nent = static_cast<long>(nstand) * nstand * npol * npol;
   if (nent == 0 || nchan == 0) return cudaSuccess;
-  dim3 grid(static_cast<unsigned>((nent + 31) / 32), (nchan + 31) / 32);
-  reorder_kernel<<<grid, dim3(32, 32), 0, stream>>>(in, reinterpret_cast<int2*>(out), a2bl, conj, nent, nchan, W,
-                                                    static_cast<long>(nchan) * W);
+  if (npol != 2) {
+    if (layout != 0) return cudaErrorInvalidValue;          // the triangular payload layouts are dual-pol only
+    dim3 grid(static_cast<unsigned>((nent + 31) / 32), (nchan + 31) / 32);
+    reorder_kernel<<<grid, dim3(32, 32), 0, stream>>>(in, reinterpret_cast<int2*>(out), a2bl, conj, nent, nchan, W,
+                                                      static_cast<long>(nchan) * W);
+    return cudaGetLastError();
+  }
+  const int nchunk = ((nstand + 1) / 2 + 31) / 32;          // 32-stand chunks per parity class
+  unsigned nblk = 0;                                        // (s1, parity, chunk) triples on or below the diagonal
+  for (int g = 0; g < 2 * nchunk; ++g) {
+    const int n = nstand - ((g & 1) + 64 * (g >> 1));
+    if (n > 0) nblk += n;
+  }
+  dim3 grid(nblk, (nchan + 31) / 32);
+  int2* o = reinterpret_cast<int2*>(out);
+  const long plane = static_cast<long>(nchan) * W;
+  switch (layout) {
+    case RO_FULL: reorder_tile_kernel<RO_FULL><<<grid, dim3(32, 32), 0, stream>>>(in, o, a2bl, conj, nstand, nchan, W, plane, nchunk); break;
+    case RO_COR: reorder_tile_kernel<RO_COR><<<grid, dim3(32, 32), 0, stream>>>(in, o, a2bl, conj, nstand, nchan, W, plane, nchunk); break;
+    case RO_PY: reorder_tile_kernel<RO_PY><<<grid, dim3(32, 32), 0, stream>>>(in, o, a2bl, conj, nstand, nchan, W, plane, nchunk); break;
+    default: return cudaErrorInvalidValue;
+  }
   return cudaGetLastError();
 }
 

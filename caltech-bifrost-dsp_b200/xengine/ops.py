@@ -105,6 +105,17 @@ def reorder(d_in, d_out, d_a2bl, d_conj, nstand, npol, nchan, wpc, stream=None):
                                    ptr(stream)), "xeng_reorder")
 
 
+PAYLOAD_COR, PAYLOAD_PY = 1, 2
+
+
+def reorder_packets(d_in, d_out, d_a2bl, d_conj, nstand, npol, nchan, wpc, layout=PAYLOAD_COR, stream=None):
+    """bfXgpuReorder fused with the per-baseline payload transpose of CorrOutputFull.send_packets_bf / _py
+    (corr_output_full_block.py:505-511, 457-460): int32 [nbl][nchan][npol][npol][2] (COR) or
+    [nbl][npol][npol][nchan][2] (PY), baselines s0 <= s1, s0-major."""
+    check(_lib.load().xeng_reorder_packets(ptr(d_in), ptr(d_out), ptr(d_a2bl), ptr(d_conj), nstand, npol, nchan, wpc,
+                                           layout, ptr(stream)), "xeng_reorder_packets")
+
+
 class Beamformer(object):
     """bfBeamformInitialize / Run / Integrate / IntegrateSingleBeam
     (beamform_block.py:251,449; beamform_sum_beams_block.py:245; beamform_sum_single_beam_block.py:114)."""

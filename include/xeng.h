@@ -95,6 +95,18 @@ int xeng_subsel(const void* d_in, void* d_out, const void* d_vismap, const void*
 int xeng_reorder(const void* d_in, void* d_out, const void* d_a2bl, const void* d_conj, int nstand, int npol,
                  int nchan, int64_t words_per_chan, void* cuda_stream);
 
+/* The same reorder, written straight into CorrOutputFull's packet payloads: one payload per baseline s0 <= s1,
+ * baselines s0-major (bl = s0*nstand - s0*(s0-1)/2 + s1 - s0), dual-pol only, d_out 16-byte aligned.
+ *   XENG_PAYLOAD_COR: int32 [nbl][nchan][npol][npol][2] -- what send_packets_bf() hands to the "cor" packet writer
+ *                     after its transpose([0,3,1,2,4]) (corr_output_full_block.py:505-511)
+ *   XENG_PAYLOAD_PY : int32 [nbl][npol][npol][nchan][2] -- reordered_data[s0, s1].tobytes() of send_packets_py()
+ *                     (corr_output_full_block.py:457-460)
+ * Half the bytes of xeng_reorder's full square matrix; nothing is left to transpose on the host. */
+#define XENG_PAYLOAD_COR 1
+#define XENG_PAYLOAD_PY 2
+int xeng_reorder_packets(const void* d_in, void* d_out, const void* d_a2bl, const void* d_conj, int nstand, int npol,
+                         int nchan, int64_t words_per_chan, int layout, void* cuda_stream);
+
 /* ------------------------------------------------------------------ Beamform / BeamformSum */
 typedef struct xeng_bf_s* xeng_bf_t;
 

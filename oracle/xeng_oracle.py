@@ -266,6 +266,19 @@ def reorder(xbuf, a2bl, conj):
     return out
 
 
+def packet_payloads(reordered, layout="cor"):
+    """Per-baseline payloads CorrOutputFull sends, from reorder()'s [s0, s1, p0, p1, chan, 2] matrix:
+    baselines s0 <= s1 in the nested-loop order of send_packets_bf / send_packets_py.
+    "cor": [nbl, nchan, npol, npol, 2] -- sdata.transpose([0,3,1,2,4]) (corr_output_full_block.py:505-511);
+    "py" : [nbl, npol, npol, nchan, 2] -- reordered_data[s0, s1].tobytes() (corr_output_full_block.py:457-460)."""
+    nstand = reordered.shape[0]
+    rows = []
+    for s0 in range(nstand):
+        sdata = reordered[s0, s0:]                      # stand x pol x pol x chan x complexity
+        rows.append(sdata.transpose([0, 3, 1, 2, 4]) if layout == "cor" else sdata)
+    return np.ascontiguousarray(np.concatenate(rows, axis=0))
+
+
 # ---------------------------------------------------------------------------
 # Beamformer
 # ---------------------------------------------------------------------------

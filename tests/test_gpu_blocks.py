@@ -185,6 +185,54 @@ def test_correlator_graph_fused_fast_dump(torch_cuda):
         assert np.array_equal(sp.view(np.int32).reshape(want.shape), want.astype(np.int32)), "slow dump %d" % k
 
 
+@pytest.mark.parametrize("use_cor_fmt", [True, False])
+def test_corr_output_full_packets(torch_cuda, use_cor_fmt):
+    """gpu-input -> Corr -> CorrAcc -> (cuda_host ring) -> CorrOutputFull: every packet's payload equals the oracle's
+    v(s0) conj(v(s1)) for that baseline in the packet's own axis order, packets come s0-major, headers carry the
+    stands (corr_output_full_block.py:440-548)."""
+    import struct
+    from xengine import ringshim
+    from xengine.blocks import Corr, CorrAcc, CorrOutputFull
+    nstand, npol, nchan, nt, ngulp = 36, 2, 40, 32, 7
+    rng = np.random.default_rng(0xc0ffee)
+    v = rng.integers(0, 256, size=(ngulp, nt, nchan, nstand, npol), dtype=np.uint8)
+    r_in = ringshim.Ring("gpu-input", space="cuda")
+    r_corr = ringshim.Ring("corr-output", space="cuda")
+    r_slow = ringshim.Ring("corr-slow-output", space="cuda_host")
+    hdr = header(nchan, nstand, npol)
+    corr = Corr(LOG, r_in, r_corr, ntime_gulp=nt, nchan=nchan, npol=npol, nstand=nstand, acc_len=nt, gpu=0,
+                autostartat=nt, ant_to_input=np.array(hdr['ant_to_input']))
+    acc = CorrAcc(LOG, r_corr, r_slow, nchan=nchan, npol=npol, nstand=nstand, acc_len=2 * nt, gpu=0,
+                  autostartat=2 * nt)
+    out = CorrOutputFull(LOG, r_slow, nchan=nchan, npol=npol, nstand=nstand, antpol_to_bl=corr.antpol_to_bl,
+                         bl_is_conj=corr.bl_is_conj, use_cor_fmt=use_cor_fmt, gpu=0)
+    packets = []
+    out.sink = lambda h, p: packets.append((h, p.copy()))
+    run_all([source(r_in, hdr, list(v)), threading.Thread(target=corr.main, name="Corr"),
+             threading.Thread(target=acc.main, name="CorrAcc"), threading.Thread(target=out.main, name="CorrOutputFull")])
+    nbl = nstand * (nstand + 1) // 2
+    assert len(packets) == 2 * nbl                     # gulps (2,3) and (4,5): two complete long integrations
+    for k in range(2):
+        fre, fim = orc.corr_full(v[2 + 2 * k])
+        f2 = orc.corr_full(v[3 + 2 * k])
+        fre, fim = fre + f2[0], fim + f2[1]            # [chan, s0, s1, p0, p1]
+        n = k * nbl
+        for s0 in range(nstand):
+            for s1 in range(s0, nstand):
+                h, p = packets[n]
+                if use_cor_fmt:
+                    assert len(h) == 32 and struct.unpack(">hh", h[28:32]) == (s0 + 1, s1 + 1)
+                    got = p.reshape(nchan, npol, npol, 2)
+                    assert np.array_equal(got[..., 0], fre[:, s0, s1]) and np.array_equal(got[..., 1], fim[:, s0, s1])
+                else:
+                    assert struct.unpack(">2I", h[-8:]) == (s0, s1)
+                    assert struct.unpack(">QQ2d4I", h[:-8])[1] == (2 + 2 * k) * nt
+                    got = p.reshape(npol, npol, nchan, 2)
+                    assert np.array_equal(got[..., 0], np.moveaxis(fre[:, s0, s1], 0, -1))
+                    assert np.array_equal(got[..., 1], np.moveaxis(fim[:, s0, s1], 0, -1))
+                n += 1
+
+
 def test_beamformer_graph_matches_oracle(torch_cuda):
     from xengine import ringshim
     from xengine.blocks import Beamform, BeamformSumBeams

@@ -173,6 +173,35 @@ def test_acc(torch_cuda, n):
     assert np.array_equal(da.cpu().numpy()[:n], (3 * b.astype(np.int64)).astype(np.int32))
 
 
+@pytest.mark.parametrize("nstand,nchan", [(12, 8), (72, 40), (132, 33), (352, 5)])
+def test_reorder_tiled_and_packet_payloads(torch_cuda, nstand, nchan):
+    """The tiled reorder (full square matrix) and the per-baseline packet payloads against the oracle, on random
+    buffer contents (the kernel is a pure permutation, so it does not need a real correlation), with a shuffled
+    antenna map for one case so nothing depends on the identity map."""
+    from xengine import ops
+    torch = torch_cuda
+    rng = np.random.default_rng(nstand * 1000 + nchan)
+    wpc = ops.words_per_chan(nstand)
+    x = rng.integers(-2**31, 2**31 - 1, size=(2, nchan, wpc), dtype=np.int64).astype(np.int32)
+    a2i = np.arange(nstand * 2, dtype=np.int32).reshape(nstand, 2)
+    if nstand == 72:
+        a2i = rng.permutation(nstand * 2).astype(np.int32).reshape(nstand, 2)
+    a2bl, conj = ops.get_order(a2i)
+    dx, da, dc = torch.from_numpy(x).cuda(), torch.from_numpy(a2bl).cuda(), torch.from_numpy(conj).cuda()
+    full = torch.full((nstand, nstand, 2, 2, nchan, 2), 0x5a5a5a5a, dtype=torch.int32, device="cuda")
+    ops.reorder(dx, full, da, dc, nstand, 2, nchan, wpc)
+    want = orc.reorder(x, a2bl, conj)
+    assert np.array_equal(full.cpu().numpy(), want)
+    nbl = nstand * (nstand + 1) // 2
+    for layout, name in ((ops.PAYLOAD_COR, "cor"), (ops.PAYLOAD_PY, "py")):
+        out = torch.full((nbl * nchan * 8,), 0x5a5a5a5a, dtype=torch.int32, device="cuda")
+        ops.reorder_packets(dx, out, da, dc, nstand, 2, nchan, wpc, layout)
+        exp = orc.packet_payloads(want, name)
+        assert np.array_equal(out.cpu().numpy().reshape(exp.shape), exp), name
+    with pytest.raises(Exception):
+        ops.reorder_packets(dx, out, da, dc, nstand, 1, nchan, wpc, ops.PAYLOAD_COR)
+
+
 def test_subsel_and_reorder(torch_cuda):
     from xengine import ops
     torch = torch_cuda

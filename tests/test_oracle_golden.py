@@ -83,6 +83,16 @@ def test_get_order_subselect_reorder_conventions(golden_dir):
     ro = orc.reorder(x, a2bl, conj)
     assert np.array_equal(ro[..., 0], np.moveaxis(gold_re, 0, -1))
     assert np.array_equal(ro[..., 1], np.moveaxis(gold_im, 0, -1))
+    # packet payloads of CorrOutputFull: one per baseline s0 <= s1, COR = [chan, pol, pol, 2], PY = [pol, pol, chan, 2]
+    cor, py = orc.packet_payloads(ro, "cor"), orc.packet_payloads(ro, "py")
+    assert cor.shape == (nstand * (nstand + 1) // 2, nchan, npol, npol, 2) and py.shape[1:] == (npol, npol, nchan, 2)
+    bl = 0
+    for s0 in range(nstand):
+        for s1 in range(s0, nstand):
+            assert np.array_equal(cor[bl, :, :, :, 0], gold_re[:, s0, s1])
+            assert np.array_equal(cor[bl, :, :, :, 1], gold_im[:, s0, s1])
+            assert py[bl].tobytes() == ro[s0, s1].tobytes()
+            bl += 1
     rng = np.random.default_rng(1)
     bls = [[[int(a), int(b)], [int(c), int(d)]] for a, b, c, d in
            zip(rng.integers(0, nstand, 50), rng.integers(0, 2, 50),
