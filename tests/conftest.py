@@ -41,6 +41,7 @@ def host_only(monkeypatch):
     monkeypatch.setattr(ops, "XCorr", fakes.FakeXCorr)
     monkeypatch.setattr(ops, "acc", fakes.fake_acc)
     monkeypatch.setattr(ops, "subsel", fakes.fake_subsel)
+    monkeypatch.setattr(ops, "reorder_packets", fakes.fake_reorder_packets)
     monkeypatch.setattr(ops, "Beamformer", fakes.FakeBeamformer)
     del fakes.CALLS[:]
     return fakes

@@ -61,6 +61,13 @@ def fake_subsel(d_in, d_out, d_vismap, d_conj, nvis, nchan, nchan_sum, wpc, stre
     CALLS.append(("subsel", int(i[0]), int(vm[0])))
 
 
+def fake_reorder_packets(d_in, d_out, d_a2bl, d_conj, nstand, npol, nchan, wpc, layout=1, stream=None):
+    i, o = _np(d_in).view(np.int32), _np(d_out).view(np.int32)
+    o[0] = i[0]                 # tag of the dump
+    o[1] = layout
+    CALLS.append(("reorder_packets", int(i[0]), int(layout), int(_np(d_a2bl).view(np.int32)[1])))
+
+
 class FakeBeamformer(object):
     def __init__(self, gpu=-1, ninput=704, nchan=192, ntime=480, nbeam=16, ntime_blocks=0, stream=None):
         self.dims = (ninput, nchan, ntime, nbeam, ntime_blocks)

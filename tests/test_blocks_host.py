@@ -321,6 +321,57 @@ def beam_cmd(beam, delays, amps, load_sample=None, seq_id="2"):
     return cmd({'coeffs': d}, seq_id)
 
 
+def test_corr_output_full_packets_headers_and_destination(host_only, tmp_path):
+    """CorrOutputFull host logic (corr_output_full_block.py:440-548,604-698): one packet per baseline s0 <= s1 in
+    nested-loop order, COR header fields / plain header fields, time tags advancing by acc_len, the tuning word,
+    `dest_file` command opening a file that receives header + payload back to back."""
+    import struct
+    from xengine.blocks import CorrOutputFull
+    matlen = NCHAN * (NSTAND // 2 + 1) * (NSTAND // 4) * NPOL * NPOL * 4
+    nbl = NSTAND * (NSTAND + 1) // 2
+    a2bl = np.arange(NSTAND * NSTAND * 4, dtype=np.int32).reshape(NSTAND, NSTAND, 2, 2) + 100
+    for cor in (True, False):
+        del host_only.CALLS[:]
+        ring = ringshim.Ring("slow", space="system")
+        hdr = base_header(seq0=40, acc_len=20, upstream_acc_len=10)
+        fill(ring, [(hdr, [gulp(3, matlen * 8), gulp(5, matlen * 8), gulp(9, 16)])])     # third span is short: skipped
+        blk = CorrOutputFull(LOG, ring, guarantee=False, nchan=NCHAN, npol=NPOL, nstand=NSTAND, antpol_to_bl=a2bl,
+                             bl_is_conj=np.zeros_like(a2bl), use_cor_fmt=cor, nchan_sum=4, pipeline_idx=5, npipeline=4)
+        assert blk.tuning == (4 << 16) | (4 << 8) | 1 and blk.igulp_size == matlen * 8
+        assert blk.dump_size == NSTAND * (NSTAND + 1) * NPOL * NPOL * NCHAN * 2 * 4 // 2
+        pkts = []
+        blk.sink = lambda h, p: pkts.append((h, p.copy()))
+        blk.main()
+        assert [c[:3] for c in host_only.CALLS] == [("reorder_packets", 3, 1 if cor else 2), ("reorder_packets", 5, 1 if cor else 2)]
+        assert host_only.CALLS[0][3] == 101                                   # the maps given to the ctor were uploaded
+        assert len(pkts) == 2 * nbl
+        assert pkts[0][1][0] == 3 and pkts[nbl][1][0] == 5                    # payload rows come from the right dump
+        assert pkts[0][1].size == NCHAN * NPOL * NPOL * 2
+        order = [(s0, s1) for s0 in range(NSTAND) for s1 in range(s0, NSTAND)]
+        spectra = int(NCHAN * hdr['fs_hz'] / hdr['bw_hz'])
+        for k, (h, _) in enumerate(pkts):
+            dump, (s0, s1) = divmod(k, nbl)[0], order[k % nbl]
+            t = 40 + 20 * dump
+            if cor:
+                sync, idf, tun, ch0, gain, tt, navg, si, sj = struct.unpack(">IIIhhqihh", h)
+                assert (sync, idf >> 24, idf & 0xFFFFFF, tun) == (0x5CDEC0DE, 2, nbl, blk.tuning)
+                assert (ch0, gain, tt, navg, si, sj) == (0, 0, t * spectra, 20 * spectra, s0 + 1, s1 + 1)
+            else:
+                f = struct.unpack(">QQ2d4I2I", h)
+                assert f == (0, t, hdr['bw_hz'], hdr['sfreq'], 20, NCHAN, 0, NPOL, s0, s1)
+    # destination file through the command interface
+    ring = ringshim.Ring("slow", space="system")
+    fill(ring, [(base_header(seq0=0, acc_len=20), [gulp(7, matlen * 8)])])
+    blk = CorrOutputFull(LOG, ring, guarantee=False, nchan=NCHAN, npol=NPOL, nstand=NSTAND, antpol_to_bl=a2bl,
+                         bl_is_conj=np.zeros_like(a2bl))
+    path = tmp_path / "cor.bin"
+    blk.process_command_strings(cmd({"dest_file": str(path)}))
+    blk.main()
+    raw = path.read_bytes()
+    assert len(raw) == nbl * (32 + NCHAN * NPOL * NPOL * 8)
+    assert struct.unpack(">hh", raw[28:32]) == (1, 1) and struct.unpack("<i", raw[32:36]) == (7,)
+
+
 def test_beamform_weights_and_load_sample(host_only):
     rng = np.random.default_rng(0xaabbccdd)
     iring, oring = ringshim.Ring("gpu-input"), ringshim.Ring("bf-output")
