@@ -41,6 +41,8 @@ def parse():
     p.add_argument("--nchan-per-gpu", type=int, default=192)
     p.add_argument("--ntime", type=int, default=480)
     p.add_argument("--acc-gulps", type=int, default=250)
+    p.add_argument("--nccl-gather", action="store_true",
+                   help="gather dumps with dist.gather (NCCL kernels) instead of copy-engine peer writes")
     p.add_argument("--cpu-seconds", type=float, default=15.0, help="budget for the cpu_baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-path-kernels", action="store_true", help="skip the per-kernel figures of the rest of the path")
@@ -116,7 +118,7 @@ def workload_config(args):
                                                                                  args.acc_gulps),
         "nchan_per_gpu": args.nchan_per_gpu, "ninput": NINPUT, "ntime_gulp": args.ntime,
         "acc_gulps": args.acc_gulps,
-        "sharding": "channel slabs, 1 rank per GPU, NCCL gather of each dump to rank 0 on a side stream (overlaps the next integration, inside the timed region)" if args.gpus > 1 else "single GPU",
+        "sharding": "channel slabs, 1 rank per GPU over torch.distributed/NCCL, each dump gathered to rank 0 on a side stream (overlaps the next integration, inside the timed region)" if args.gpus > 1 else "single GPU",
         "l2": "inputs rotate over 4 distinct gulps (>=260 MB) and every step read-modify-writes the 383 MB "
               "accumulator, both larger than the 126 MB L2",
     }
@@ -322,7 +324,7 @@ def run_b200(args):
     d_acc = torch.zeros(out_words, dtype=torch.int32, device=dev)
     d_dump = torch.zeros(out_words, dtype=torch.int32, device=dev)
     gather_list = None
-    if world > 1 and rank == 0:
+    if world > 1 and rank == 0 and args.nccl_gather:
         gather_list = [d_dump] + [torch.empty_like(d_dump) for _ in range(world - 1)]
     stream = torch.cuda.Stream(device=dev)
     xc = ops.XCorr(nstand=NSTAND, npol=NPOL, nchan=nchan, ntime_gulp=ntime, gpu=local)
@@ -334,6 +336,10 @@ def run_b200(args):
         torch.cuda.synchronize(dev)
 
     gstream = torch.cuda.Stream(device=dev) if world > 1 else None
+    peer = None
+    if world > 1 and not args.nccl_gather:
+        peer = sharding.PeerGather(out_words, torch.int32, dev, dist, root=0)
+        d_dump = peer.slot if rank == 0 else d_dump        # rank 0 snapshots straight into its own slot
 
     def dump_device():
         # CorrAcc's copy_array into its output span, then (N > 1) the NCCL gather of that span to rank 0 on a side
@@ -345,7 +351,10 @@ def run_b200(args):
         if world > 1:
             gstream.wait_stream(stream)
             with torch.cuda.stream(gstream):
-                sharding.gather_to_root(d_dump, dist, root=0, out=gather_list)
+                if peer is not None:
+                    peer.push(d_dump)
+                else:
+                    sharding.gather_to_root(d_dump, dist, root=0, out=gather_list)
 
     def step_device(i):
         xc.accumulate(d_in[i % NBUF], d_acc, (i % accg) == 0)
@@ -399,6 +408,18 @@ def run_b200(args):
         dmp1.record(stream)
     barrier()
     dump_ms = dmp0.elapsed_time(dmp1)
+    gather_ok = None
+    if world > 1:                                           # what arrived on rank 0 is what each rank sent
+        probe = torch.stack([d_dump[:4096].to(torch.int64).sum(), d_dump[-4096:].to(torch.int64).sum()])
+        sent = [torch.empty_like(probe) for _ in range(world)]
+        dist.all_gather(sent, probe)
+        if rank == 0:
+            got = peer.parts() if peer is not None else gather_list
+            gather_ok = all(bool((torch.stack([got[r][:4096].to(torch.int64).sum(),
+                                               got[r][-4096:].to(torch.int64).sum()]) == sent[r]).all())
+                            for r in range(world))
+            if not gather_ok:
+                raise RuntimeError("gathered dump on rank 0 differs from what the ranks sent")
 
     # ---- e2e: host (pinned) voltages in, dump to pinned host memory out, copies inside the timed region
     h_in = [torch.empty((ntime, nchan, NINPUT), dtype=torch.uint8).pin_memory() for _ in range(2)]
@@ -487,10 +508,12 @@ def run_b200(args):
                     "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": d2h_total / K,
                     "ms_per_step": e2e_ms / K, "checksum": checksum},
             "gpu_launches": K,
-            "dump": {"in_timed_region": ndump, "every_steps": accg, "alone_ms": dump_ms,
+            "dump": {"in_timed_region": ndump, "every_steps": accg, "alone_ms": dump_ms, "gather_verified": gather_ok,
+                     "gather": None if world == 1 else ("NCCL dist.gather" if args.nccl_gather else
+                                                        "peer writes into rank 0's symmetric-memory buffer (copy engines over NVLink)"),
                      "bytes_to_rank0": (world - 1) * out_words * 4,
                      "note": "dumps fall at their true cadence (every acc_gulps steps); alone_ms is one dump "
-                             "(device copy + NCCL gather to rank 0) timed with nothing to overlap"},
+                             "(device copy + gather to rank 0) timed with nothing to overlap"},
             "roofline": {"kernel": "corr_swz_kernel (fused Corr+CorrAcc)", "bound": "hbm", "achieved": achieved,
                          "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
                          "traffic_source": traffic_src,
