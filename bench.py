@@ -324,8 +324,6 @@ def run_b200(args):
     d_acc = torch.zeros(out_words, dtype=torch.int32, device=dev)
     d_dump = torch.zeros(out_words, dtype=torch.int32, device=dev)
     gather_list = None
-    if world > 1 and rank == 0 and args.nccl_gather:
-        gather_list = [d_dump] + [torch.empty_like(d_dump) for _ in range(world - 1)]
     stream = torch.cuda.Stream(device=dev)
     xc = ops.XCorr(nstand=NSTAND, npol=NPOL, nchan=nchan, ntime_gulp=ntime, gpu=local)
     xc.set_stream(stream)
@@ -338,8 +336,19 @@ def run_b200(args):
     gstream = torch.cuda.Stream(device=dev) if world > 1 else None
     peer = None
     if world > 1 and not args.nccl_gather:
-        peer = sharding.PeerGather(out_words, torch.int32, dev, dist, root=0)
-        d_dump = peer.slot if rank == 0 else d_dump        # rank 0 snapshots straight into its own slot
+        try:
+            peer = sharding.PeerGather(out_words, torch.int32, dev, dist, root=0)
+        except Exception as e:                              # no symmetric memory on this node: all ranks use NCCL
+            sys.stderr.write("rank %d: PeerGather unavailable (%s)\n" % (rank, e))
+        agreed = torch.tensor([1 if peer is not None else 0], device=dev)
+        dist.all_reduce(agreed, op=dist.ReduceOp.MIN)
+        if int(agreed) == 0:
+            peer, args.nccl_gather = None, True
+        else:
+            d_dump = peer.slot if rank == 0 else d_dump    # rank 0 snapshots straight into its own slot
+
+    if world > 1 and rank == 0 and args.nccl_gather:
+        gather_list = [d_dump] + [torch.empty_like(d_dump) for _ in range(world - 1)]
 
     def dump_device():
         # CorrAcc's copy_array into its output span, then (N > 1) the NCCL gather of that span to rank 0 on a side

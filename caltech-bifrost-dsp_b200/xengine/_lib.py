@@ -41,6 +41,7 @@ SIGNATURES = {
     "xeng_acc": (_i, [_vp, _vp, _sz, _i, _vp]),
     "xeng_subsel": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _vp]),
     "xeng_reorder": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _vp]),
+    "xeng_subsel_packets": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _i, _vp]),
     "xeng_reorder_packets": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _i, _vp]),
     "xeng_bf_create": (_i, [C.POINTER(_vp), _i, _i, _i, _i, _i, _i]),
     "xeng_bf_destroy": (_i, [_vp]),

@@ -4,6 +4,7 @@ from .corr_block import Corr  # noqa: F401
 from .corr_acc_block import CorrAcc  # noqa: F401
 from .corr_subsel_block import CorrSubsel  # noqa: F401
 from .corr_output_full_block import CorrOutputFull  # noqa: F401
+from .corr_output_part_block import CorrOutputPart  # noqa: F401
 from .beamform_block import Beamform  # noqa: F401
 from .beamform_sum_beams_block import BeamformSumBeams  # noqa: F401
 from .beamform_sum_block import BeamformSum  # noqa: F401

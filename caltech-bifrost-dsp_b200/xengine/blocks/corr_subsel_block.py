@@ -19,8 +19,13 @@ class CorrSubsel(Block):
     nvis_out = 48 * 49 * 4 // 2     # 48 stands, dual pol: 4704 (corr_subsel_block.py:185)
 
     def __init__(self, log, iring, oring, guarantee=True, core=-1, etcd_client=None, nchan=192, npol=2, nstand=352,
-                 nchan_sum=4, gpu=-1, antpol_to_bl=None, bl_is_conj=None):
+                 nchan_sum=4, gpu=-1, antpol_to_bl=None, bl_is_conj=None, payload_layout=None):
         super(CorrSubsel, self).__init__(log, iring, oring, guarantee, core, etcd_client=etcd_client)
+        # optional, not in the reference: write the span in CorrOutputPart's packet order ('py' | 'cor') on the
+        # device instead of the ring layout, announced by the header key ``payload_layout``
+        if payload_layout not in (None, 'py', 'cor'):
+            raise ValueError("payload_layout must be None, 'py' or 'cor'")
+        self.payload_layout = payload_layout
         self.nchan_in = nchan
         self.nchan_out = nchan // nchan_sum
         self.nchan_sum = nchan_sum
@@ -87,6 +92,8 @@ class CorrSubsel(Block):
                 ohdr['sfreq'] = (ihdr['sfreq'] + ((self.nchan_sum - 1) * chan_width)) / self.nchan_sum
                 self._load_selection(ohdr)                   # a new sequence always picks up the latest selection
                 ohdr['nchan_sum'] = self.nchan_sum
+                if self.payload_layout:
+                    ohdr['payload_layout'] = self.payload_layout
                 oseq = oring.begin_sequence(time_tag=time_tag, header=json.dumps(ohdr), nringlet=iseq.nringlet)
                 time_tag += 1
                 for ispan in iseq.read(self.igulp_size):
@@ -98,8 +105,13 @@ class CorrSubsel(Block):
                         t = time.time()
                         reserve_time, prev = t - prev, t
                         try:
-                            ops.subsel(ispan.data, self.obuf_gpu, self._subsel, self._conj, self.nvis_out,
-                                       self.nchan_in, self.nchan_sum, self.words_per_chan)
+                            if self.payload_layout:
+                                ops.subsel_packets(ispan.data, self.obuf_gpu, self._subsel, self._conj, self.nvis_out,
+                                                   self.nchan_in, self.nchan_sum, self.words_per_chan,
+                                                   ops.PAYLOAD_PY if self.payload_layout == 'py' else ops.PAYLOAD_COR)
+                            else:
+                                ops.subsel(ispan.data, self.obuf_gpu, self._subsel, self._conj, self.nvis_out,
+                                           self.nchan_in, self.nchan_sum, self.words_per_chan)
                         except Exception as e:
                             self.log.error("xeng_subsel failed: %s" % e)
                             raise RuntimeError(str(e))

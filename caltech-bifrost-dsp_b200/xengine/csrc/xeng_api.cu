@@ -312,13 +312,13 @@ int xeng_corr_accumulate_subsel(xeng_corr_t h, const void* d_in, void* d_acc, in
   XENG_CUDA(xeng::launch_acc(static_cast<int32_t*>(d_acc), h->d_sub_scratch, words, first ? 1 : 0, h->stream));
   if (sub_first) {
     XENG_CUDA(xeng::launch_subsel(h->d_sub_scratch, so, h->d_sub_vismap, h->d_sub_conj, h->sub_nvis, h->nchan,
-                                  h->sub_nsum, h->words_per_chan, h->stream));
+                                  h->sub_nsum, h->words_per_chan, 0, h->stream));
   } else {      // sub_out += sel(X): select into the (now free) head of the scratch buffer, then add
     const size_t nsel = static_cast<size_t>(2) * h->sub_nvis * (h->nchan / h->sub_nsum);
     int32_t* tmp = nullptr;
     XENG_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&tmp), nsel * sizeof(int32_t), h->stream));
     XENG_CUDA(xeng::launch_subsel(h->d_sub_scratch, tmp, h->d_sub_vismap, h->d_sub_conj, h->sub_nvis, h->nchan,
-                                  h->sub_nsum, h->words_per_chan, h->stream));
+                                  h->sub_nsum, h->words_per_chan, 0, h->stream));
     XENG_CUDA(xeng::launch_acc(so, tmp, nsel, 0, h->stream));
     XENG_CUDA(cudaFreeAsync(tmp, h->stream));
   }
@@ -387,7 +387,19 @@ int xeng_subsel(const void* d_in, void* d_out, const void* d_vismap, const void*
   if (nvis < 0 || nchan <= 0 || nchan_sum <= 0 || words_per_chan <= 0) return fail(XENG_ERR_ARG, "bad sizes");
   XENG_CUDA(xeng::launch_subsel(static_cast<const int32_t*>(d_in), static_cast<int32_t*>(d_out),
                                 static_cast<const int32_t*>(d_vismap), static_cast<const int32_t*>(d_conj), nvis,
-                                nchan, nchan_sum, words_per_chan, static_cast<cudaStream_t>(stream)));
+                                nchan, nchan_sum, words_per_chan, 0, static_cast<cudaStream_t>(stream)));
+  return XENG_OK;
+}
+
+int xeng_subsel_packets(const void* d_in, void* d_out, const void* d_vismap, const void* d_conj, int nvis, int nchan,
+                        int nchan_sum, int64_t words_per_chan, int layout, void* stream) {
+  if (!d_in || !d_out || !d_vismap || !d_conj) return fail(XENG_ERR_ARG, "null pointer");
+  if (nvis < 0 || nchan <= 0 || nchan_sum <= 0 || words_per_chan <= 0) return fail(XENG_ERR_ARG, "bad sizes");
+  if (layout != XENG_PAYLOAD_COR && layout != XENG_PAYLOAD_PY) return fail(XENG_ERR_ARG, "unknown payload layout");
+  if (layout == XENG_PAYLOAD_COR && (nvis & 3)) return fail(XENG_ERR_ARG, "COR packets hold 4 visibilities: 4 | nvis");
+  XENG_CUDA(xeng::launch_subsel(static_cast<const int32_t*>(d_in), static_cast<int32_t*>(d_out),
+                                static_cast<const int32_t*>(d_vismap), static_cast<const int32_t*>(d_conj), nvis,
+                                nchan, nchan_sum, words_per_chan, layout, static_cast<cudaStream_t>(stream)));
   return XENG_OK;
 }
 

@@ -46,6 +46,11 @@ __global__ void acc_tail_kernel(int32_t* __restrict__ acc, const int32_t* __rest
 // CorrSubsel: out[c', v] = sum_{k < nchan_sum} X[c'*nchan_sum + k][vismap[v]], imag negated where conj[v]
 // (bfXgpuSubSelect, call site corr_subsel_block.py:298; semantics pinned by
 // pipeline/verification/test_corr_part_rx.py:38-49,76-84).  Output re/im interleaved (corr_subsel_block.py:302).
+// LAYOUT 0: [chan'][vis][2], the ring layout above.  The other two are the payloads CorrOutputPart builds from it on
+// the host: 1 = "COR" packets [vis/4][chan'][4][2] (send_packets_bf's dview.transpose([1,0,2,3]),
+// corr_output_part_block.py:378-391); 2 = plain packets [vis][chan'][2] in big-endian words (dout, dtype '>i',
+// corr_output_part_block.py:429,460-463).
+template <int LAYOUT>
 __global__ void __launch_bounds__(256) subsel_kernel(const int32_t* __restrict__ in, int2* __restrict__ out,
                                                      const int32_t* __restrict__ vismap,
                                                      const int32_t* __restrict__ conj, int nvis, int nchan_out,
@@ -61,7 +66,9 @@ __global__ void __launch_bounds__(256) subsel_kernel(const int32_t* __restrict__
     im += __ldg(p + plane_words + k * W);
   }
   if (conj[v]) im = -im;
-  out[static_cast<long>(co) * nvis + v] = make_int2(re, im);
+  if (LAYOUT == 0) out[static_cast<long>(co) * nvis + v] = make_int2(re, im);
+  if (LAYOUT == 1) out[(static_cast<long>(v >> 2) * nchan_out + co) * 4 + (v & 3)] = make_int2(re, im);
+  if (LAYOUT == 2) out[static_cast<long>(v) * nchan_out + co] = make_int2(__byte_perm(re, 0, 0x0123), __byte_perm(im, 0, 0x0123));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -208,12 +215,18 @@ cudaError_t launch_acc(int32_t* acc, const int32_t* in, size_t n, int first, cud
 }
 
 cudaError_t launch_subsel(const int32_t* in, int32_t* out, const int32_t* vismap, const int32_t* conj, int nvis,
-                          int nchan, int nchan_sum, long W, cudaStream_t stream) {
+                          int nchan, int nchan_sum, long W, int layout, cudaStream_t stream) {
   const int nchan_out = nchan / nchan_sum;
   if (nvis <= 0 || nchan_out <= 0) return cudaSuccess;
   dim3 grid((nvis + 255) / 256, nchan_out);
-  subsel_kernel<<<grid, 256, 0, stream>>>(in, reinterpret_cast<int2*>(out), vismap, conj, nvis, nchan_out, nchan_sum, W,
-                                          static_cast<long>(nchan) * W);
+  int2* o = reinterpret_cast<int2*>(out);
+  const long plane = static_cast<long>(nchan) * W;
+  switch (layout) {
+    case 0: subsel_kernel<0><<<grid, 256, 0, stream>>>(in, o, vismap, conj, nvis, nchan_out, nchan_sum, W, plane); break;
+    case 1: subsel_kernel<1><<<grid, 256, 0, stream>>>(in, o, vismap, conj, nvis, nchan_out, nchan_sum, W, plane); break;
+    case 2: subsel_kernel<2><<<grid, 256, 0, stream>>>(in, o, vismap, conj, nvis, nchan_out, nchan_sum, W, plane); break;
+    default: return cudaErrorInvalidValue;
+  }
   return cudaGetLastError();
 }
 

@@ -108,6 +108,13 @@ def reorder(d_in, d_out, d_a2bl, d_conj, nstand, npol, nchan, wpc, stream=None):
 PAYLOAD_COR, PAYLOAD_PY = 1, 2
 
 
+def subsel_packets(d_in, d_out, d_vismap, d_conj, nvis, nchan, nchan_sum, wpc, layout=PAYLOAD_PY, stream=None):
+    """bfXgpuSubSelect written in CorrOutputPart's packet order (corr_output_part_block.py:378-391, 429-463):
+    COR = int32 [nvis/4][nchan/nchan_sum][4][2]; PY = big-endian int32 [nvis][nchan/nchan_sum][2]."""
+    check(_lib.load().xeng_subsel_packets(ptr(d_in), ptr(d_out), ptr(d_vismap), ptr(d_conj), nvis, nchan, nchan_sum,
+                                          wpc, layout, ptr(stream)), "xeng_subsel_packets")
+
+
 def reorder_packets(d_in, d_out, d_a2bl, d_conj, nstand, npol, nchan, wpc, layout=PAYLOAD_COR, stream=None):
     """bfXgpuReorder fused with the per-baseline payload transpose of CorrOutputFull.send_packets_bf / _py
     (corr_output_full_block.py:505-511, 457-460): int32 [nbl][nchan][npol][npol][2] (COR) or

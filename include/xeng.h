@@ -104,6 +104,13 @@ int xeng_reorder(const void* d_in, void* d_out, const void* d_a2bl, const void* 
  * Half the bytes of xeng_reorder's full square matrix; nothing is left to transpose on the host. */
 #define XENG_PAYLOAD_COR 1
 #define XENG_PAYLOAD_PY 2
+/* xeng_subsel written straight into CorrOutputPart's packet payloads (same XENG_PAYLOAD_* constants):
+ *   XENG_PAYLOAD_COR: int32 [nvis/4][nchan/nchan_sum][4][2] -- send_packets_bf()'s dview.transpose([1,0,2,3])
+ *                     (corr_output_part_block.py:378-391); needs 4 | nvis
+ *   XENG_PAYLOAD_PY : big-endian int32 [nvis][nchan/nchan_sum][2] -- `dout`, dtype '>i'
+ *                     (corr_output_part_block.py:429,460-463) */
+int xeng_subsel_packets(const void* d_in, void* d_out, const void* d_vismap, const void* d_conj, int nvis, int nchan,
+                        int nchan_sum, int64_t words_per_chan, int layout, void* cuda_stream);
 int xeng_reorder_packets(const void* d_in, void* d_out, const void* d_a2bl, const void* d_conj, int nstand, int npol,
                          int nchan, int64_t words_per_chan, int layout, void* cuda_stream);
 

@@ -266,6 +266,21 @@ def reorder(xbuf, a2bl, conj):
     return out
 
 
+def subsel_packet_payloads(sub, layout="py"):
+    """CorrOutputPart's payloads from CorrSubsel's [nchan, nvis, 2] span.
+    "py" : big-endian [nvis, nchan, 2] -- idata.transpose([1,0,2]) copied into dout (dtype '>i')
+           (corr_output_part_block.py:429,460-463); returned as the raw bytes viewed as uint8.
+    "cor": [nvis/4, nchan, 4, 2] -- dview = data.reshape([nchan, nvis//4, 2, 2]) then transpose([1,0,2,3])
+           (corr_output_part_block.py:378-391)."""
+    nchan, nvis, _ = sub.shape
+    if layout == "py":
+        dout = np.zeros([nvis, nchan, 2], dtype=">i")
+        dout[...] = sub.transpose([1, 0, 2])
+        return np.frombuffer(dout.tobytes(), dtype=np.uint8)
+    dview = sub.reshape([nchan, nvis // 4, 2, 2, 2])
+    return np.ascontiguousarray(dview.transpose([1, 0, 2, 3, 4])).reshape(nvis // 4, nchan, 4, 2)
+
+
 def packet_payloads(reordered, layout="cor"):
     """Per-baseline payloads CorrOutputFull sends, from reorder()'s [s0, s1, p0, p1, chan, 2] matrix:
     baselines s0 <= s1 in the nested-loop order of send_packets_bf / send_packets_py.

@@ -233,6 +233,63 @@ def test_corr_output_full_packets(torch_cuda, use_cor_fmt):
                 n += 1
 
 
+@pytest.mark.parametrize("use_cor_fmt,device_layout", [(False, True), (True, True), (False, False), (True, False)])
+def test_corr_output_part_packets(torch_cuda, use_cor_fmt, device_layout):
+    """gpu-input -> Corr -> CorrSubsel -> (cuda_host ring) -> CorrOutputPart, with the payload order produced on the
+    device (payload_layout) or by the block's host transpose: same packets either way, each equal to the oracle's
+    channel-summed v(s0,p0) conj(v(s1,p1)) (corr_output_part_block.py:346-401; test_corr_part_rx.py:76-84)."""
+    import struct
+    from xengine import ringshim
+    from xengine.blocks import Corr, CorrSubsel, CorrOutputPart
+    nstand, npol, nchan, nt, ngulp, ncs = 16, 2, 8, 32, 4, 2
+    rng = np.random.default_rng(0xbead)
+    v = rng.integers(0, 256, size=(ngulp, nt, nchan, nstand, npol), dtype=np.uint8)
+    r_in = ringshim.Ring("gpu-input", space="cuda")
+    r_corr = ringshim.Ring("corr-output", space="cuda")
+    r_fast = ringshim.Ring("corr-fast-output", space="cuda_host")
+    hdr = header(nchan, nstand, npol)
+    corr = Corr(LOG, r_in, r_corr, ntime_gulp=nt, nchan=nchan, npol=npol, nstand=nstand, acc_len=nt, gpu=0,
+                autostartat=nt, ant_to_input=np.array(hdr['ant_to_input']))
+    layout = ('cor' if use_cor_fmt else 'py') if device_layout else None
+    sub = CorrSubsel(LOG, r_corr, r_fast, nchan=nchan, npol=npol, nstand=nstand, nchan_sum=ncs, gpu=0,
+                     antpol_to_bl=corr.antpol_to_bl, bl_is_conj=corr.bl_is_conj, payload_layout=layout)
+    # all dual-pol baselines of the first 48 stands' worth of slots: 4704 = 48*49/2 * 4, stands taken modulo nstand
+    bls = []
+    for i in range(48):
+        for j in range(i, 48):
+            for p0 in range(2):
+                for p1 in range(2):
+                    bls.append([[i % nstand, p0], [j % nstand, p1]])
+    assert len(bls) == sub.nvis_out
+    sub.process_command_strings(json.dumps({"id": "1", "cmd": "update", "val": {"kwargs": {"baselines": bls}}}))
+    out = CorrOutputPart(LOG, r_fast, use_cor_fmt=use_cor_fmt, nvis_per_packet=16, nchan_sum=ncs)
+    packets = []
+    out.sink = lambda h, p: packets.append((h, p))
+    run_all([source(r_in, hdr, list(v)), threading.Thread(target=corr.main, name="Corr"),
+             threading.Thread(target=sub.main, name="CorrSubsel"), threading.Thread(target=out.main, name="CorrOutputPart")])
+    nco = nchan // ncs
+    per_dump = sub.nvis_out // 4 if use_cor_fmt else sub.nvis_out // 16
+    assert len(packets) == 3 * per_dump                 # gulps 1, 2, 3
+    for k in range(3):
+        fre, fim = orc.corr_full(v[1 + k])
+        fre = fre.reshape(nco, ncs, nstand, nstand, 2, 2).sum(1)
+        fim = fim.reshape(nco, ncs, nstand, nstand, 2, 2).sum(1)
+        for n in (0, 1, per_dump // 2, per_dump - 1):
+            h, p = packets[k * per_dump + n]
+            if use_cor_fmt:
+                got = np.frombuffer(p, dtype=np.int32).reshape(nco, 4, 2)
+                vis = bls[4 * n:4 * n + 4]
+                assert len(h) == 32
+            else:
+                got = np.frombuffer(p, dtype='>i4').reshape(16, nco, 2).transpose(1, 0, 2)
+                vis = bls[16 * n:16 * n + 16]
+                assert np.frombuffer(h[struct.calcsize(">QQ2d4I"):], dtype='>i4').reshape(16, 2, 2).tolist() == vis
+                assert struct.unpack(">QQ2d4I", h[:struct.calcsize(">QQ2d4I")])[1] == (1 + k) * nt
+            for m, ((s0, p0), (s1, p1)) in enumerate(vis):
+                assert np.array_equal(got[:, m, 0], fre[:, s0, s1, p0, p1])
+                assert np.array_equal(got[:, m, 1], fim[:, s0, s1, p0, p1])
+
+
 def test_beamformer_graph_matches_oracle(torch_cuda):
     from xengine import ringshim
     from xengine.blocks import Beamform, BeamformSumBeams

@@ -238,6 +238,17 @@ def test_subsel_and_reorder(torch_cuda):
         for k, ((s0, p0), (s1, p1)) in enumerate(bls[:50]):
             assert np.array_equal(got[:, k, 0], fre[:, s0, s1, p0, p1].reshape(-1, ncs).sum(1))
             assert np.array_equal(got[:, k, 1], fim[:, s0, s1, p0, p1].reshape(-1, ncs).sum(1))
+    # the same selection written in CorrOutputPart's packet orders (corr_output_part_block.py:378-391, 429-463)
+    nv = 300
+    want = orc.subselect(x, vm[:nv], cj[:nv], 2)
+    dvm, dcj = torch.from_numpy(vm[:nv].copy()).cuda(), torch.from_numpy(cj[:nv].copy()).cuda()
+    for layout, name in ((ops.PAYLOAD_PY, "py"), (ops.PAYLOAD_COR, "cor")):
+        o = torch.zeros(nchan // 2 * nv * 2, dtype=torch.int32, device="cuda")
+        ops.subsel_packets(dx, o, dvm, dcj, nv, nchan, 2, ops.words_per_chan(nstand), layout)
+        exp = orc.subsel_packet_payloads(want, name)
+        assert o.cpu().numpy().tobytes() == exp.tobytes(), name
+    with pytest.raises(Exception):
+        ops.subsel_packets(dx, o, dvm, dcj, 301, nchan, 2, ops.words_per_chan(nstand), ops.PAYLOAD_COR)
 
 
 @pytest.mark.parametrize("shape,ncs,impl", [

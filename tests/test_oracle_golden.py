@@ -102,6 +102,13 @@ def test_get_order_subselect_reorder_conventions(golden_dir):
     for n, ((s0, p0), (s1, p1)) in enumerate(bls):
         assert out[0, n, 0] == gold_re[:, s0, s1, p0, p1].sum()
         assert out[0, n, 1] == gold_im[:, s0, s1, p0, p1].sum()
+    # CorrOutputPart payloads: plain = big-endian [vis, chan, 2]; COR = [vis/4, chan, 4, 2]
+    sub = orc.subselect(x, vm[:48], cj[:48], nchan_sum=1)
+    raw = orc.subsel_packet_payloads(sub, "py")
+    assert np.array_equal(np.frombuffer(raw.tobytes(), dtype=">i4").reshape(48, nchan, 2), sub.transpose(1, 0, 2))
+    corp = orc.subsel_packet_payloads(sub, "cor")
+    for v in (0, 5, 47):
+        assert np.array_equal(corp[v // 4, :, v % 4], sub[:, v])
 
 
 def test_corr_accumulates_over_gulps(golden_dir):
