@@ -282,6 +282,10 @@ def path_kernels(torch, ops, dev, nchan, hbm_peak, iters=10):
     ms = timeit(lambda: bf.integrate(bo, po, nsum))
     ab = bo.numel() * 4 + po.numel() * 4
     res["beamform_sum"] = {"ms": ms, "alg_bytes": ab, "gbs": ab / ms / 1e6, "frac_hbm": ab / ms / 1e6 / hbm_peak}
+    # configs[3] as one kernel: power integration in the beamformer's epilogue, voltage beams never written
+    ms_f = timeit(lambda: bf.run_integrate(vv, po, w, nsum))
+    res["beamform_power_fused"] = {"ms": ms_f, "gsamples_per_s": nt * nchan * NINPUT / ms_f / 1e6,
+                                   "tflops_fp32": fl / ms_f / 1e9, "unfused_ms": res["beamform"]["ms"] + ms}
     bf.close()
     return res
 

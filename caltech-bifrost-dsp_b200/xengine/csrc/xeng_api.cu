@@ -66,7 +66,8 @@ struct xeng_corr_s {
 struct xeng_bf_s {
   int device, ninput, nchan, ntime, nbeam, ntime_blocks;
   cudaStream_t stream;
-  float2* d_volt;   // scratch voltage beams for xeng_bf_run_integrate
+  float2* d_volt;   // scratch voltage beams for xeng_bf_run_integrate when the voltage tap is on
+  int tap;          // xeng_bf_set_tap: keep the voltage beams (two kernels) instead of the fused power epilogue
 };
 
 extern "C" {
@@ -438,6 +439,7 @@ int xeng_bf_create(xeng_bf_t* out, int gpu, int ninput, int nchan, int ntime, in
   h->ninput = ninput; h->nchan = nchan; h->ntime = ntime; h->nbeam = nbeam; h->ntime_blocks = ntime_blocks;
   h->stream = nullptr;
   h->d_volt = nullptr;
+  h->tap = 0;
   cudaError_t e = cudaGetDevice(&h->device);
   if (e != cudaSuccess) {
     delete h;
@@ -476,12 +478,28 @@ int xeng_bf_run_integrate(xeng_bf_t h, const void* d_in, void* d_out, const void
   if (!h || !d_in || !d_out || !d_w) return fail(XENG_ERR_ARG, "null pointer");
   if (ntime_sum <= 0 || (h->nbeam & 1) || h->ntime % ntime_sum) return fail(XENG_ERR_ARG, "need ntime_sum | ntime and an even number of beams");
   XENG_CUDA(cudaSetDevice(h->device));
+  if (!h->tap && ntime_sum <= xeng::beamform_fused_max_ntime_sum()) {   // one kernel, only the powers leave the SM
+    xeng::BeamArgs a;
+    a.in = static_cast<const uint8_t*>(d_in);
+    a.w = static_cast<const float2*>(d_w);
+    a.out = nullptr;
+    a.ntime = h->ntime; a.nchan = h->nchan; a.ninput = h->ninput; a.nbeam = h->nbeam;
+    a.pow_out = static_cast<float*>(d_out);
+    a.ntime_sum = ntime_sum;
+    XENG_CUDA(xeng::launch_beamform(a, h->stream));
+    return XENG_OK;
+  }
   if (!h->d_volt) XENG_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->d_volt), sizeof(float2) * h->nchan * h->nbeam * static_cast<size_t>(h->ntime)));
   int rc = xeng_bf_run(h, d_in, h->d_volt, d_w);
   if (rc) return rc;
   return xeng_bf_integrate(h, h->d_volt, d_out, ntime_sum);
 }
 const void* xeng_bf_voltages(xeng_bf_t h) { return h ? h->d_volt : nullptr; }
+int xeng_bf_set_tap(xeng_bf_t h, int on) {
+  if (!h) return fail(XENG_ERR_ARG, "null handle");
+  h->tap = on ? 1 : 0;
+  return XENG_OK;
+}
 
 int xeng_bf_integrate(xeng_bf_t h, const void* d_in, void* d_out, int ntime_sum) {
   if (!h || !d_in || !d_out) return fail(XENG_ERR_ARG, "null pointer");

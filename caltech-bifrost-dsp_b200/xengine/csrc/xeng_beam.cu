@@ -49,11 +49,16 @@ __device__ __forceinline__ float2 decode44(uint32_t byte) {
   return make_float2(static_cast<float>(re), static_cast<float>(im));
 }
 
+// FUSED: the |B|^2 integration of BeamformSumBeams runs in the epilogue and only the powers leave the SM.  The CTA
+// then owns tile_t = the largest multiple of ntime_sum that fits in TT samples (120 of 128 for ntime_sum = 24: the
+// same number of CTAs along time for a 960-sample gulp) so that every integration block lies inside one CTA; the
+// per-sample products and the time-ordered sums are the expressions of beam_integrate_kernel below.
+template <bool FUSED>
 __global__ void __launch_bounds__(BF_THREADS, 2) beamform_kernel(BeamArgs a) {
   extern __shared__ __align__(16) uint8_t bf_smem[];
   BeamSmem& S = *reinterpret_cast<BeamSmem*>(bf_smem);
   const int tid = threadIdx.x;
-  const int t0 = blockIdx.x * TT, c = blockIdx.y, b0 = blockIdx.z * BB;
+  const int t0 = blockIdx.x * (FUSED ? a.tile_t : TT), c = blockIdx.y, b0 = blockIdx.z * BB;
   const int tb = tid >> 5, tt = tid & 31;
 
   // staging roles
@@ -142,6 +147,33 @@ __global__ void __launch_bounds__(BF_THREADS, 2) beamform_kernel(BeamArgs a) {
     }
   }
 
+  if (FUSED) {
+    __syncthreads();                                       // every warp is done with S.v: reuse it for the products
+    float4* prod = reinterpret_cast<float4*>(&S.v[0][0]);  // [BB / 2 dual-pol beams][TT samples], 32 KB
+#pragma unroll
+    for (int jp = 0; jp < 2; ++jp) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 x = acc[2 * jp][k], y = acc[2 * jp + 1][k];
+        prod[(2 * tb + jp) * TT + 4 * tt + k] =
+            make_float4(x.x * x.x + x.y * x.y, y.x * y.x + y.y * y.y, x.x * y.x + x.y * y.y, x.y * y.x - x.x * y.y);
+      }
+    }
+    __syncthreads();
+    const int nblk = a.ntime / a.ntime_sum, per_cta = a.tile_t / a.ntime_sum, T0 = t0 / a.ntime_sum;
+    float4* pout = reinterpret_cast<float4*>(a.pow_out);
+    for (int idx = tid; idx < (BB / 2) * per_cta; idx += BF_THREADS) {
+      const int pair = idx / per_cta, Tl = idx - pair * per_cta;
+      if (T0 + Tl >= nblk || b0 + 2 * pair + 1 >= a.nbeam) continue;
+      float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4* q = prod + pair * TT + Tl * a.ntime_sum;
+      for (int k = 0; k < a.ntime_sum; ++k) {
+        sum.x += q[k].x; sum.y += q[k].y; sum.z += q[k].z; sum.w += q[k].w;
+      }
+      pout[(static_cast<long>(b0 / 2 + pair) * nblk + T0 + Tl) * a.nchan + c] = sum;
+    }
+    return;
+  }
   const int t = t0 + 4 * tt;
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
@@ -211,16 +243,30 @@ __global__ void __launch_bounds__(256) beam_integrate_kernel(const float2* __res
 cudaError_t launch_beamform(const BeamArgs& a, cudaStream_t stream) {
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(beamform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(beamform_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(sizeof(BeamSmem)));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(beamform_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               static_cast<int>(sizeof(BeamSmem)));
     if (e != cudaSuccess) return e;
     configured = true;
   }
   if (a.ntime <= 0 || a.nchan <= 0 || a.nbeam <= 0) return cudaSuccess;
+  if (a.pow_out) {                                          // fused power integration
+    if (a.ntime_sum <= 0 || a.ntime_sum > TT || (a.nbeam & 1)) return cudaErrorInvalidValue;
+    BeamArgs f = a;
+    f.tile_t = (TT / a.ntime_sum) * a.ntime_sum;
+    const int nt = (a.ntime / a.ntime_sum) * a.ntime_sum;   // whole integration blocks only
+    if (nt == 0) return cudaSuccess;
+    dim3 grid((nt + f.tile_t - 1) / f.tile_t, a.nchan, (a.nbeam + BB - 1) / BB);
+    beamform_kernel<true><<<grid, BF_THREADS, sizeof(BeamSmem), stream>>>(f);
+    return cudaGetLastError();
+  }
   dim3 grid((a.ntime + TT - 1) / TT, a.nchan, (a.nbeam + BB - 1) / BB);
-  beamform_kernel<<<grid, BF_THREADS, sizeof(BeamSmem), stream>>>(a);
+  beamform_kernel<false><<<grid, BF_THREADS, sizeof(BeamSmem), stream>>>(a);
   return cudaGetLastError();
 }
+int beamform_fused_max_ntime_sum() { return TT; }
 
 cudaError_t launch_beam_integrate(const float2* in, float* out, int nchan, int nbeam, int ntime, int ntime_sum,
                                   int beam0, int nbeam_out, cudaStream_t stream) {

@@ -49,8 +49,11 @@ struct BeamArgs {
   const float2* w;     // [nchan][nbeam][ninput]
   float2* out;         // [nchan][nbeam][ntime]
   int ntime, nchan, ninput, nbeam;
+  float* pow_out = nullptr;   // non-null: fused power integration, [nbeam/2][ntime/ntime_sum][nchan][4]; `out` unused
+  int ntime_sum = 0, tile_t = 0;
 };
 cudaError_t launch_beamform(const BeamArgs& a, cudaStream_t stream);
+int beamform_fused_max_ntime_sum();
 cudaError_t launch_beam_integrate(const float2* in, float* out, int nchan, int nbeam, int ntime, int ntime_sum,
                                   int beam0, int nbeam_out, cudaStream_t stream);
 

@@ -141,8 +141,12 @@ class Beamformer(object):
     def run(self, d_in, d_out, d_weights):
         check(self._lib.xeng_bf_run(self._h, ptr(d_in), ptr(d_out), ptr(d_weights)), "xeng_bf_run")
 
+    def set_tap(self, on):
+        """Keep the voltage beams of run_integrate in the handle (two kernels) instead of the fused power epilogue."""
+        check(self._lib.xeng_bf_set_tap(self._h, int(bool(on))), "xeng_bf_set_tap")
+
     def run_integrate(self, d_in, d_out, d_weights, ntime_sum):
-        """Beamform's ntime_sum mode: voltages stay in the handle, integrated powers go to d_out."""
+        """Beamform's ntime_sum mode: integrated powers go to d_out; one fused kernel for ntime_sum <= 128."""
         check(self._lib.xeng_bf_run_integrate(self._h, ptr(d_in), ptr(d_out), ptr(d_weights), int(ntime_sum)),
               "xeng_bf_run_integrate")
 

@@ -131,11 +131,14 @@ int xeng_bf_integrate(xeng_bf_t h, const void* d_in, void* d_out, int ntime_sum)
  * d_out f32 [ntime/ntime_sum][nchan][4] for dual-pol beam beam_id. */
 int xeng_bf_integrate_single(xeng_bf_t h, const void* d_in, void* d_out, int ntime_sum, int beam_id);
 /* Beamform's ntime_sum != None mode (beamform_block.py:216-218,249-251: bfBeamformInitialize with ntime_blocks > 0,
- * then bfBeamformRun emits integrated powers): d_out f32 [nbeam/2][ntime/ntime_sum][nchan][4]; the voltage beams
- * stay in a handle-owned scratch buffer (also readable through xeng_bf_voltages for a VLBI-style tap). */
+ * then bfBeamformRun emits integrated powers): d_out f32 [nbeam/2][ntime/ntime_sum][nchan][4].  For ntime_sum <= 128
+ * this is ONE kernel: the power integration runs in the beamformer's epilogue and the voltage beams never reach
+ * HBM.  With the tap on (or a longer ntime_sum) it is the beamformer followed by the integration kernel, the voltage
+ * beams staying in a handle-owned scratch buffer readable through xeng_bf_voltages (a VLBI-style tap). */
 int xeng_bf_run_integrate(xeng_bf_t h, const void* d_in, void* d_out, const void* d_weights, int ntime_sum);
-/* Device pointer of the handle-owned cf32 [nchan][nbeam][ntime] voltage scratch (NULL before the first
- * xeng_bf_run_integrate). */
+int xeng_bf_set_tap(xeng_bf_t h, int on);
+/* Device pointer of the handle-owned cf32 [nchan][nbeam][ntime] voltage scratch (NULL until an
+ * xeng_bf_run_integrate with the tap on has run). */
 const void* xeng_bf_voltages(xeng_bf_t h);
 int xeng_bf_sync(xeng_bf_t h);
 
