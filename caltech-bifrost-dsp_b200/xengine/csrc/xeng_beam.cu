@@ -120,10 +120,12 @@ __global__ void __launch_bounds__(BF_THREADS, 2) beamform_kernel(BeamArgs a) {
       float4 wv[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) wv[j] = *reinterpret_cast<const float4*>(&S.w[4 * tb + j][i]);
-      const float4 va0 = *reinterpret_cast<const float4*>(&S.v[i][4 * tt]);
-      const float4 va1 = *reinterpret_cast<const float4*>(&S.v[i][4 * tt + 2]);
-      const float4 vb0 = *reinterpret_cast<const float4*>(&S.v[i + 1][4 * tt]);
-      const float4 vb1 = *reinterpret_cast<const float4*>(&S.v[i + 1][4 * tt + 2]);
+      // a thread's four samples are {2tt, 2tt+1, 64+2tt, 64+2tt+1}: each LDS.128 of a warp is 512 contiguous bytes
+      // (4 wavefronts; samples 4tt..4tt+3 would put the lanes 32 B apart and cost 8)
+      const float4 va0 = *reinterpret_cast<const float4*>(&S.v[i][2 * tt]);
+      const float4 va1 = *reinterpret_cast<const float4*>(&S.v[i][TT / 2 + 2 * tt]);
+      const float4 vb0 = *reinterpret_cast<const float4*>(&S.v[i + 1][2 * tt]);
+      const float4 vb1 = *reinterpret_cast<const float4*>(&S.v[i + 1][TT / 2 + 2 * tt]);
       const float2 va[4] = {make_float2(va0.x, va0.y), make_float2(va0.z, va0.w), make_float2(va1.x, va1.y),
                             make_float2(va1.z, va1.w)};
       const float2 vb[4] = {make_float2(vb0.x, vb0.y), make_float2(vb0.z, vb0.w), make_float2(vb1.x, vb1.y),
@@ -155,7 +157,7 @@ __global__ void __launch_bounds__(BF_THREADS, 2) beamform_kernel(BeamArgs a) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const float2 x = acc[2 * jp][k], y = acc[2 * jp + 1][k];
-        prod[(2 * tb + jp) * TT + 4 * tt + k] =
+        prod[(2 * tb + jp) * TT + (k >> 1) * (TT / 2) + 2 * tt + (k & 1)] =
             make_float4(x.x * x.x + x.y * x.y, y.x * y.x + y.y * y.y, x.x * y.x + x.y * y.y, x.y * y.x - x.x * y.y);
       }
     }
@@ -174,19 +176,21 @@ __global__ void __launch_bounds__(BF_THREADS, 2) beamform_kernel(BeamArgs a) {
     }
     return;
   }
-  const int t = t0 + 4 * tt;
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     const int b = b0 + 4 * tb + j;
     if (b >= a.nbeam) continue;
-    float2* o = a.out + (static_cast<long>(c) * a.nbeam + b) * a.ntime + t;
-    if (t + 3 < a.ntime && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
-      reinterpret_cast<float4*>(o)[0] = make_float4(acc[j][0].x, acc[j][0].y, acc[j][1].x, acc[j][1].y);
-      reinterpret_cast<float4*>(o)[1] = make_float4(acc[j][2].x, acc[j][2].y, acc[j][3].x, acc[j][3].y);
-    } else {
 #pragma unroll
-      for (int k = 0; k < 4; ++k)
-        if (t + k < a.ntime) o[k] = acc[j][k];
+    for (int h = 0; h < 2; ++h) {                          // the two sample pairs of the thread
+      const int t = t0 + h * (TT / 2) + 2 * tt;
+      float2* o = a.out + (static_cast<long>(c) * a.nbeam + b) * a.ntime + t;
+      if (t + 1 < a.ntime && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+        *reinterpret_cast<float4*>(o) = make_float4(acc[j][2 * h].x, acc[j][2 * h].y, acc[j][2 * h + 1].x, acc[j][2 * h + 1].y);
+      } else {
+#pragma unroll
+        for (int k = 0; k < 2; ++k)
+          if (t + k < a.ntime) o[k] = acc[j][2 * h + k];
+      }
     }
   }
 }
