@@ -13,3 +13,10 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
 timeout 300 $SHORT > gpurun_out/${TAG}_plain2.log 2>&1 && \
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:corr_ -s 3 -c 2 \
     -f -o gpurun_out/${TAG}_corr $SHORT > gpurun_out/${TAG}_ncu2.log 2>&1; echo "ncu full rc=$?"
+# duration + DRAM bytes of every other path kernel (CorrAcc, CorrSubsel, reorder, Beamform, BeamformSum)
+timeout 300 python scripts/prof_path.py > gpurun_out/${TAG}_path_plain.log 2>&1 && \
+timeout 600 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none \
+    -k regex:"acc_kernel|subsel_kernel|reorder_tile|beamform_kernel|beam_integrate" -c 40 --csv \
+    --log-file gpurun_out/${TAG}_path_kernels.csv python scripts/prof_path.py > gpurun_out/${TAG}_ncu3.log 2>&1; echo "ncu path rc=$?"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:beamform_kernel -s 2 -c 1 \
+    -f -o gpurun_out/${TAG}_beam python scripts/prof_beam.py > gpurun_out/${TAG}_ncu4.log 2>&1; echo "ncu beam rc=$?"

@@ -87,5 +87,25 @@ def full(src, dst):
             json.dump(out, f, indent=1)
 
 
+def path(src, dst):
+    """duration + DRAM bytes per launch (second launch of each kernel: warm instruction cache, cold data)."""
+    rows = read_csv_after_header(open(src).read(), "ID")
+    per = collections.OrderedDict()
+    for r in rows:
+        val = float(r["Metric Value"].replace(",", ""))
+        unit = r.get("Metric Unit", "")
+        val *= {"ns": 1.0, "us": 1e3, "ms": 1e6, "byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1.0)
+        per.setdefault(r["ID"], {"name": r["Kernel Name"][:70]})[r["Metric Name"]] = val
+    with open(dst, "w") as f:
+        f.write("source: %s (ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum "
+                "--clock-control none; python scripts/prof_path.py)\n" % src)
+        f.write("id | kernel | us | dram_read_MB | dram_write_MB | dram_GB/s\n")
+        for k, m in per.items():
+            us = m.get("gpu__time_duration.sum", 0) / 1e3
+            rd, wr = m.get("dram__bytes_read.sum", 0) / 1e6, m.get("dram__bytes_write.sum", 0) / 1e6
+            f.write("%s | %s | %.1f | %.1f | %.1f | %.0f\n" % (k, m["name"], us, rd, wr, (rd + wr) / max(us, 1e-9) * 1e3))
+    sys.stdout.write(open(dst).read())
+
+
 if __name__ == "__main__":
-    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2], sys.argv[3])
+    {"launches": launches, "full": full, "path": path}[sys.argv[1]](sys.argv[2], sys.argv[3])
