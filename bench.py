@@ -14,6 +14,7 @@ import argparse
 import json
 import os
 import subprocess
+import struct
 import sys
 import tempfile
 import time
@@ -269,6 +270,25 @@ def path_kernels(torch, ops, dev, nchan, hbm_peak, iters=10):
     res["corr_acc_subsel_fused"]["unfused_ms"] = ms_store + res["corr_acc"]["ms"] + res["corr_subsel_4704"]["ms"]
     xc.close()
     del gulps, acc2, fast
+    # ingest: one gulp of SNAP2 packets (96 ch x 64 inputs each, 22 per spectrum) -> voltage buffer
+    ncp, npp, stride = 96, 64, 32 + 96 * 64
+    npk = ntime * (nchan // ncp) * (NINPUT // npp)
+    hdr = np.zeros((npk, 32), dtype=np.uint8)
+    k = 0
+    for t in range(ntime):
+        for cb in range(nchan // ncp):
+            for pb in range(NINPUT // npp):
+                hdr[k] = np.frombuffer(struct.pack('>QLHHHHLLL', 7000 + t, 0, npp, NINPUT, ncp, nchan, cb, cb * ncp, pb * npp),
+                                       dtype=np.uint8)
+                k += 1
+    raw = torch.randint(0, 256, (npk, stride), dtype=torch.uint8, device=dev)
+    raw[:, :32] = torch.from_numpy(hdr).to(dev)
+    vbuf = torch.zeros((ntime, nchan, NINPUT), dtype=torch.uint8, device=dev)
+    ms = timeit(lambda: ops.snap2_assemble(raw, npk, stride, vbuf, 7000, ntime, nchan, NINPUT, 0, False))
+    ab = 2 * ntime * nchan * NINPUT
+    res["snap2_assemble"] = {"ms": ms, "packets": npk, "alg_bytes": ab, "gbs": ab / ms / 1e6,
+                             "frac_hbm": ab / ms / 1e6 / hbm_peak, "gsamples_per_s": ntime * nchan * NINPUT / ms / 1e6}
+    del raw, vbuf
     nbeam, nt, nsum = 32, 960, 24
     bf = ops.Beamformer(ninput=NINPUT, nchan=nchan, ntime=nt, nbeam=nbeam)
     vv = torch.randint(0, 256, (nt, nchan, NINPUT), dtype=torch.uint8, device=dev)

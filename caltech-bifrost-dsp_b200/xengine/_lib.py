@@ -19,7 +19,7 @@ class XengError(RuntimeError):
 
 _lib = None
 
-_vp, _i, _i64, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_size_t
+_vp, _i, _i64, _sz, _u64 = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_uint64
 
 # name -> (restype, argtypes); must list every symbol include/xeng.h declares
 SIGNATURES = {
@@ -41,6 +41,7 @@ SIGNATURES = {
     "xeng_acc": (_i, [_vp, _vp, _sz, _i, _vp]),
     "xeng_subsel": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _vp]),
     "xeng_reorder": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _vp]),
+    "xeng_snap2_assemble": (_i, [_vp, _i, _i64, _vp, _u64, _i, _i, _i, _i, _i, _vp, _vp]),
     "xeng_subsel_packets": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _i, _vp]),
     "xeng_reorder_packets": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _i, _vp]),
     "xeng_bf_create": (_i, [C.POINTER(_vp), _i, _i, _i, _i, _i, _i]),

@@ -427,6 +427,23 @@ int xeng_reorder_packets(const void* d_in, void* d_out, const void* d_a2bl, cons
   return XENG_OK;
 }
 
+// ------------------------------------------------------------------------------------ ingest
+int xeng_snap2_assemble(const void* d_pkts, int npkt, int64_t pkt_stride, void* d_out, uint64_t seq0, int ntime,
+                        int nchan, int ninput, int first_chan, int zero_first, void* d_nvalid, void* stream) {
+  if (!d_out || (npkt > 0 && !d_pkts)) return fail(XENG_ERR_ARG, "null pointer");
+  if (npkt < 0 || pkt_stride < 32 || ntime <= 0 || nchan <= 0 || ninput <= 0 || first_chan < 0)
+    return fail(XENG_ERR_ARG, "bad sizes");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (zero_first) {      // samples of packets that never arrive read as zero, as bifrost's capture leaves them
+    XENG_CUDA(cudaMemsetAsync(d_out, 0, static_cast<size_t>(ntime) * nchan * ninput, st));
+    if (d_nvalid) XENG_CUDA(cudaMemsetAsync(d_nvalid, 0, sizeof(int), st));
+  }
+  XENG_CUDA(xeng::launch_snap2_assemble(static_cast<const uint8_t*>(d_pkts), npkt, pkt_stride,
+                                        static_cast<uint8_t*>(d_out), seq0, ntime, nchan, ninput, first_chan,
+                                        static_cast<int*>(d_nvalid), st));
+  return XENG_OK;
+}
+
 // ------------------------------------------------------------------------------------ Beamform
 int xeng_bf_create(xeng_bf_t* out, int gpu, int ninput, int nchan, int ntime, int nbeam, int ntime_blocks) {
   if (!out) return fail(XENG_ERR_ARG, "null handle pointer");

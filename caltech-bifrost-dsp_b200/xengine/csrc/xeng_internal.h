@@ -52,6 +52,8 @@ struct BeamArgs {
   float* pow_out = nullptr;   // non-null: fused power integration, [nbeam/2][ntime/ntime_sum][nchan][4]; `out` unused
   int ntime_sum = 0, tile_t = 0;
 };
+cudaError_t launch_snap2_assemble(const uint8_t* pkts, int npkt, long pkt_stride, uint8_t* out, unsigned long long seq0,
+                                  int ntime, int nchan, int ninput, int first_chan, int* nvalid, cudaStream_t stream);
 cudaError_t launch_beamform(const BeamArgs& a, cudaStream_t stream);
 int beamform_fused_max_ntime_sum();
 cudaError_t launch_beam_integrate(const float2* in, float* out, int nchan, int nbeam, int ntime, int ntime_sum,

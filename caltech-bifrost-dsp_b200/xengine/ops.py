@@ -106,6 +106,16 @@ def reorder(d_in, d_out, d_a2bl, d_conj, nstand, npol, nchan, wpc, stream=None):
 
 
 PAYLOAD_COR, PAYLOAD_PY = 1, 2
+SNAP2_HEADER_BYTES = 32
+
+
+def snap2_assemble(d_pkts, npkt, pkt_stride, d_out, seq0, ntime, nchan, ninput, first_chan=0, zero_first=True,
+                   d_nvalid=None, stream=None):
+    """SNAP2 packets (device copy of the raw receive buffer) -> u8 [ntime][nchan][ninput] voltages; the host-side
+    counterpart in the reference is bifrost's UDP capture behind Capture (capture_block.py:219-305)."""
+    check(_lib.load().xeng_snap2_assemble(ptr(d_pkts), int(npkt), int(pkt_stride), ptr(d_out), int(seq0), int(ntime),
+                                          int(nchan), int(ninput), int(first_chan), int(bool(zero_first)),
+                                          ptr(d_nvalid), ptr(stream)), "xeng_snap2_assemble")
 
 
 def subsel_packets(d_in, d_out, d_vismap, d_conj, nvis, nchan, nchan_sum, wpc, layout=PAYLOAD_PY, stream=None):

@@ -114,6 +114,18 @@ int xeng_subsel_packets(const void* d_in, void* d_out, const void* d_vismap, con
 int xeng_reorder_packets(const void* d_in, void* d_out, const void* d_a2bl, const void* d_conj, int nstand, int npol,
                          int nchan, int64_t words_per_chan, int layout, void* cuda_stream);
 
+/* ------------------------------------------------------------------ ingest */
+/* SNAP2 F-engine packets -> the u8 [ntime][nchan][ninput] voltage buffer, on the device.  Replaces the per-row
+ * host memcpy of bifrost's UDP capture behind Capture (capture_block.py:219-305); packet = 32-byte big-endian header
+ * (u64 seq, u32 sync_time, u16 npol, u16 npol_tot, u16 nchan, u16 nchan_tot, u32 chan_block_id, u32 chan0, u32 pol0)
+ * + u8 [nchan][npol] (test_transmitters/test_tx.c:27-42, test_tx_vectors.py:37-47,103-109).
+ * d_pkts: npkt raw packets pkt_stride bytes apart (device memory); out[seq - seq0][chan0 - first_chan + c][pol0 + p]
+ * = payload[c][p].  Packets outside [seq0, seq0 + ntime) x [first_chan, first_chan + nchan) x [0, ninput) are
+ * dropped; d_nvalid (device int32, optional) counts the accepted ones.  zero_first clears d_out (and d_nvalid)
+ * first, so samples of lost packets read as zero. */
+int xeng_snap2_assemble(const void* d_pkts, int npkt, int64_t pkt_stride, void* d_out, uint64_t seq0, int ntime,
+                        int nchan, int ninput, int first_chan, int zero_first, void* d_nvalid, void* cuda_stream);
+
 /* ------------------------------------------------------------------ Beamform / BeamformSum */
 typedef struct xeng_bf_s* xeng_bf_t;
 

@@ -266,6 +266,35 @@ def reorder(xbuf, a2bl, conj):
     return out
 
 
+def snap2_packet(seq, sync_time, npol, npol_tot, nchan, nchan_tot, chan_block_id, chan0, pol0, payload):
+    """One SNAP2 F-engine packet as the reference's transmitters build it: struct.pack('>QLHHHHLLL', ...) + payload
+    u8 [nchan][npol] (pipeline/test_transmitters/test_tx_vectors.py:37-47,103-109; test_tx.c:27-42)."""
+    import struct
+    return struct.pack('>QLHHHHLLL', seq, sync_time, npol, npol_tot, nchan, nchan_tot, chan_block_id, chan0, pol0) + \
+        np.ascontiguousarray(payload, dtype=np.uint8).tobytes()
+
+
+def snap2_assemble(packets, seq0, ntime, nchan, ninput, first_chan=0):
+    """What the capture leaves in the gpu-input ring for a window of spectra: out[seq - seq0][chan0 - first_chan + c]
+    [pol0 + p] = payload[c][p], zeros where no packet arrived, packets outside the window dropped
+    (capture_block.py:219-305 + the header above).  Returns (u8 [ntime, nchan, ninput], accepted packet count)."""
+    import struct
+    out = np.zeros((ntime, nchan, ninput), dtype=np.uint8)
+    ngood = 0
+    for pkt in packets:
+        seq, _, npol, _, pn, _, _, chan0, pol0 = struct.unpack('>QLHHHHLLL', pkt[:32])
+        if not (seq0 <= seq < seq0 + ntime):
+            continue
+        if npol <= 0 or pn <= 0 or chan0 < first_chan or chan0 + pn > first_chan + nchan or pol0 + npol > ninput:
+            continue
+        if 32 + pn * npol > len(pkt):
+            continue
+        data = np.frombuffer(pkt, dtype=np.uint8, count=pn * npol, offset=32).reshape(pn, npol)
+        out[seq - seq0, chan0 - first_chan:chan0 - first_chan + pn, pol0:pol0 + npol] = data
+        ngood += 1
+    return out, ngood
+
+
 def subsel_packet_payloads(sub, layout="py"):
     """CorrOutputPart's payloads from CorrSubsel's [nchan, nvis, 2] span.
     "py" : big-endian [nvis, nchan, 2] -- idata.transpose([1,0,2]) copied into dout (dtype '>i')
