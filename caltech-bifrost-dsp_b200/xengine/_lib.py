@@ -53,6 +53,7 @@ SIGNATURES = {
     "xeng_bf_run_integrate": (_i, [_vp, _vp, _vp, _vp, _i]),
     "xeng_bf_voltages": (_vp, [_vp]),
     "xeng_bf_set_tap": (_i, [_vp, _i]),
+    "xeng_bf_vlbi_tap": (_i, [_vp, _vp, _vp, _i]),
     "xeng_bf_sync": (_i, [_vp]),
 }
 

@@ -527,6 +527,15 @@ int xeng_bf_integrate(xeng_bf_t h, const void* d_in, void* d_out, int ntime_sum)
   return XENG_OK;
 }
 
+int xeng_bf_vlbi_tap(xeng_bf_t h, const void* d_in, void* d_out, int nbeam_send) {
+  if (!h || !d_in || !d_out) return fail(XENG_ERR_ARG, "null pointer");
+  if (nbeam_send <= 0 || nbeam_send > h->nbeam) return fail(XENG_ERR_ARG, "need 0 < nbeam_send <= nbeam");
+  XENG_CUDA(cudaSetDevice(h->device));
+  XENG_CUDA(xeng::launch_vlbi_tap(static_cast<const float2*>(d_in), static_cast<float2*>(d_out), h->nchan, h->nbeam,
+                                  h->ntime, nbeam_send, h->stream));
+  return XENG_OK;
+}
+
 int xeng_bf_integrate_single(xeng_bf_t h, const void* d_in, void* d_out, int ntime_sum, int beam_id) {
   if (!h || !d_in || !d_out) return fail(XENG_ERR_ARG, "null pointer");
   if (ntime_sum <= 0 || beam_id < 0 || 2 * beam_id + 1 >= h->nbeam) return fail(XENG_ERR_ARG, "bad ntime_sum / beam_id");

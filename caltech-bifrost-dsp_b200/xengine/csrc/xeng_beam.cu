@@ -242,7 +242,32 @@ __global__ void __launch_bounds__(256) beam_integrate_kernel(const float2* __res
   }
 }
 
+// BeamformVlbiOutput's tap: the first nsend voltage beams, [chan][beam][time] -> [time][chan][beam]
+// (idata[:, 0:nsend, :].transpose([2,0,1]), beamform_vlbi_output_block.py:260-264).  32 channels x 32 samples per
+// block through shared memory: reads run along time, writes along (chan, beam).
+__global__ void __launch_bounds__(1024) vlbi_tap_kernel(const float2* __restrict__ in, float2* __restrict__ out,
+                                                        int nchan, int nbeam, int ntime, int nsend) {
+  __shared__ float2 tile[32][33];
+  const int c0 = blockIdx.y * 32, t0 = blockIdx.x * 32;
+  for (int b = 0; b < nsend; ++b) {
+    const int c = c0 + threadIdx.y, t = t0 + threadIdx.x;
+    if (c < nchan && t < ntime) tile[threadIdx.y][threadIdx.x] = in[(static_cast<long>(c) * nbeam + b) * ntime + t];
+    __syncthreads();
+    const int co = c0 + threadIdx.x, to = t0 + threadIdx.y;
+    if (co < nchan && to < ntime) out[(static_cast<long>(to) * nchan + co) * nsend + b] = tile[threadIdx.x][threadIdx.y];
+    __syncthreads();
+  }
+}
+
 }  // namespace
+
+cudaError_t launch_vlbi_tap(const float2* in, float2* out, int nchan, int nbeam, int ntime, int nsend,
+                            cudaStream_t stream) {
+  if (nchan <= 0 || ntime <= 0 || nsend <= 0) return cudaSuccess;
+  dim3 grid((ntime + 31) / 32, (nchan + 31) / 32);
+  vlbi_tap_kernel<<<grid, dim3(32, 32), 0, stream>>>(in, out, nchan, nbeam, ntime, nsend);
+  return cudaGetLastError();
+}
 
 cudaError_t launch_beamform(const BeamArgs& a, cudaStream_t stream) {
   static bool configured = false;

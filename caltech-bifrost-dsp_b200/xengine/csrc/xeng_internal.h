@@ -56,6 +56,8 @@ cudaError_t launch_snap2_assemble(const uint8_t* pkts, int npkt, long pkt_stride
                                   int ntime, int nchan, int ninput, int first_chan, int* nvalid, cudaStream_t stream);
 cudaError_t launch_beamform(const BeamArgs& a, cudaStream_t stream);
 int beamform_fused_max_ntime_sum();
+cudaError_t launch_vlbi_tap(const float2* in, float2* out, int nchan, int nbeam, int ntime, int nsend,
+                            cudaStream_t stream);
 cudaError_t launch_beam_integrate(const float2* in, float* out, int nchan, int nbeam, int ntime, int ntime_sum,
                                   int beam0, int nbeam_out, cudaStream_t stream);
 

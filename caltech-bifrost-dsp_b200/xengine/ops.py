@@ -167,6 +167,10 @@ class Beamformer(object):
         check(self._lib.xeng_bf_integrate_single(self._h, ptr(d_in), ptr(d_out), int(ntime_sum), int(beam_id)),
               "xeng_bf_integrate_single")
 
+    def vlbi_tap(self, d_in, d_out, nbeam_send):
+        """First nbeam_send voltage beams as [ntime][nchan][nbeam_send] (beamform_vlbi_output_block.py:260-264)."""
+        check(self._lib.xeng_bf_vlbi_tap(self._h, ptr(d_in), ptr(d_out), int(nbeam_send)), "xeng_bf_vlbi_tap")
+
     def sync(self):
         check(self._lib.xeng_bf_sync(self._h), "xeng_bf_sync")
 

@@ -152,6 +152,10 @@ int xeng_bf_set_tap(xeng_bf_t h, int on);
 /* Device pointer of the handle-owned cf32 [nchan][nbeam][ntime] voltage scratch (NULL until an
  * xeng_bf_run_integrate with the tap on has run). */
 const void* xeng_bf_voltages(xeng_bf_t h);
+/* BeamformVlbiOutput's voltage tap (beamform_vlbi_output_block.py:260-264: idata[:, 0:nsend, :] copied to the host
+ * and transposed to time x chan x beam there): d_in cf32 [nchan][nbeam][ntime] -> d_out cf32 [ntime][nchan][nbeam_send],
+ * on the device. */
+int xeng_bf_vlbi_tap(xeng_bf_t h, const void* d_in, void* d_out, int nbeam_send);
 int xeng_bf_sync(xeng_bf_t h);
 
 #ifdef __cplusplus
