@@ -332,12 +332,24 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
         const int gs = gs0 + ks;
         const int rs = gs % RAW_STAGES, slot = gs % NSTAGE;
         XTRACE(grp, 0);
-        mbar_wait(&S->raw_full[rs], (gs / RAW_STAGES) & 1, a.err, 500 + rs);
+        const bool ldg_path = ABL && (ablate & 64);                    // ablation: global -> registers, no raw ring
+        if (!ldg_path) mbar_wait(&S->raw_full[rs], (gs / RAW_STAGES) & 1, a.err, 500 + rs);
         XTRACE(grp, 1);
         const uint32_t rbase = raw0 + rs * RAW_STAGE_BYTES;
         const bool live = kb * 32 < a.ntime - ks * ST_T;               // this K-block holds samples (else: not issued)
         uint4 rawA0, rawA1, rawB0, rawB1;
         rawA0 = rawA1 = rawB0 = rawB1 = make_uint4(0u, 0u, 0u, 0u);
+        if (ldg_path) {
+          if (live) {   // timing only: no bounds handling (rows past ninput read the next channel's bytes)
+            const long t = ks * ST_T + kb * 32 + wg * 8 + tlow;
+            const uint8_t* g = a.in + (min(t, static_cast<long>(a.ntime - 1)) * a.nchan + tl.c) * a.ninput + 32 * c;
+            const int ia = min(tl.I * TILE, a.ninput - TILE), ib = min(tl.J * TILE, a.ninput - TILE);
+            rawA0 = __ldg(reinterpret_cast<const uint4*>(g + ia));
+            rawA1 = __ldg(reinterpret_cast<const uint4*>(g + ia + 16));
+            rawB0 = __ldg(reinterpret_cast<const uint4*>(g + ib));
+            rawB1 = __ldg(reinterpret_cast<const uint4*>(g + ib + 16));
+          }
+        } else {
         if (live) {
           rawA0 = lds_v4(rbase + lds_a);
           rawA1 = lds_v4(rbase + lds_b);
@@ -347,6 +359,7 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
         // The TMA warp may refill the raw slot once the loads have RETURNED, not merely issued (SYNCS.ARRIVE does
         // not wait for outstanding LDS): make the arrive depend on one word of every load.
         mbar_arrive_after(&S->raw_empty[rs], scratch, rawA0.x ^ rawA1.x ^ rawB0.x ^ rawB1.x);
+        }
         const uint32_t base = stages0 + slot * STAGE_BYTES;
         uint4 reA0, imA0, reA1, imA1, reB0, imB0, reB1, imB1, nimB0, nimB1;
         if (live) {
@@ -388,7 +401,7 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
     if (kb == 0 && wg == 0 && lane == 0) XTRACE_DUMP(grp);
   } else if (warp == WARP_TMA) {
     // ===================================================================== TMA producer (one lane)
-    if (lane == 0) {
+    if (lane == 0 && !(ABL && (ablate & 64))) {
       int gs = 0;
       for (TileWalk tw(a); tw.valid(a); tw.next(a)) {
         const Tile tl = tw.get();

@@ -1,5 +1,7 @@
 """Developer tool: time the fused Corr+CorrAcc kernel with parts of it switched off (XENG_CORR_ABLATE bit mask:
-1 no global write, 2 no epilogue staging stores, 4 no MMA issue, 8 no operand stores by the unpack warps).
+1 no global write, 2 no epilogue staging stores, 4 no MMA issue, 8 no operand stores by the unpack warps,
+16 no nibble arithmetic, 32 no TMA loads, 64 unpack warps read global memory directly (LDG, no raw ring, no TMA)).
+Needs a library built with -DXENG_CT_ABLATE=1 (XENG_LIB_PATH points at it).
 Results of ablated runs are invalid by construction; only the timings matter."""
 import os
 import sys
