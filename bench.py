@@ -307,6 +307,25 @@ def path_kernels(torch, ops, dev, nchan, hbm_peak, iters=10):
     res["beamform_power_fused"] = {"ms": ms_f, "gsamples_per_s": nt * nchan * NINPUT / ms_f / 1e6,
                                    "tflops_fp32": fl / ms_f / 1e9, "unfused_ms": res["beamform"]["ms"] + ms}
     bf.close()
+    del vv, w, bo, po
+    # offline upchannelise path at the scripts' sizes: 480-sample gulp = 15 frames x 32 fine samples,
+    # 96 ch (lwa352-upchan-bf.py:86-87, --nchan default), 4 beams (--nbeam default)
+    nfr, nf, nch_u, nb_u = 15, 32, 96, 4
+    vu = torch.randint(0, 256, (nfr, nf, nch_u, NINPUT), dtype=torch.uint8, device=dev)
+    xu = torch.zeros((nfr, nch_u, NINPUT, nf, 2), dtype=torch.float32, device=dev)
+    wu = torch.randn((nb_u, nch_u, NINPUT, nf, 2), dtype=torch.float32, device=dev)
+    ou = torch.zeros((nfr, nb_u, nch_u, nf, 2), dtype=torch.float32, device=dev)
+    nsamp = nfr * nf * nch_u * NINPUT
+    for name, lay in (("upchan_fft_fine_last", ops.UPCHAN_FINE_LAST), ("upchan_fft_freq_merged", ops.UPCHAN_FREQ_MERGED)):
+        ms = timeit(lambda: ops.upchan_fft(vu, xu, nfr, nf, nch_u, NINPUT, lay))
+        ab = 9 * nsamp
+        res[name] = {"ms": ms, "alg_bytes": ab, "gbs": ab / ms / 1e6, "frac_hbm": ab / ms / 1e6 / hbm_peak,
+                     "gsamples_per_s": nsamp / ms / 1e6}
+    ms = timeit(lambda: ops.upchan_beamform(vu, wu, ou, nfr, nf, nch_u, NINPUT, nb_u))
+    ab = nsamp + wu.numel() * 4 + ou.numel() * 4
+    res["upchan_beamform_fused"] = {"ms": ms, "alg_bytes": ab, "gbs": ab / ms / 1e6,
+                                    "frac_hbm": ab / ms / 1e6 / hbm_peak, "gsamples_per_s": nsamp / ms / 1e6,
+                                    "config": "%d frames x %d fine x %d ch x %d inputs, %d beams" % (nfr, nf, nch_u, NINPUT, nb_u)}
     return res
 
 

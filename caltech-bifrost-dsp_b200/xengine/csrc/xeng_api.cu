@@ -444,6 +444,38 @@ int xeng_snap2_assemble(const void* d_pkts, int npkt, int64_t pkt_stride, void* 
   return XENG_OK;
 }
 
+// ------------------------------------------------------------------------------------ offline upchannelise
+static int upchan_check(const void* a, const void* b, int nframe, int nfine, int nchan, int ninput) {
+  if (!a || !b) return fail(XENG_ERR_ARG, "null pointer");
+  if (nframe < 0 || nchan <= 0 || ninput <= 0) return fail(XENG_ERR_ARG, "bad sizes");
+  if (nfine != 2 && nfine != 4 && nfine != 8 && nfine != 16 && nfine != 32)
+    return fail(XENG_ERR_ARG, "nfine must be 2, 4, 8, 16 or 32");
+  return XENG_OK;
+}
+
+int xeng_upchan_fft(const void* d_in, void* d_out, int nframe, int nfine, int nchan, int ninput, int layout,
+                    void* stream) {
+  int rc = upchan_check(d_in, d_out, nframe, nfine, nchan, ninput);
+  if (rc) return rc;
+  if (layout != XENG_UPCHAN_FINE_LAST && layout != XENG_UPCHAN_FREQ_MERGED) return fail(XENG_ERR_ARG, "bad layout");
+  if (static_cast<long>(nframe) * nchan > 2147483647L) return fail(XENG_ERR_ARG, "nframe * nchan too large");
+  XENG_CUDA(xeng::launch_upchan_fft(static_cast<const uint8_t*>(d_in), static_cast<float2*>(d_out), nframe, nfine,
+                                    nchan, ninput, layout, static_cast<cudaStream_t>(stream)));
+  return XENG_OK;
+}
+
+int xeng_upchan_beamform(const void* d_in, const void* d_weights, void* d_out, int nframe, int nfine, int nchan,
+                         int ninput, int nbeam, void* stream) {
+  int rc = upchan_check(d_in, d_out, nframe, nfine, nchan, ninput);
+  if (rc) return rc;
+  if (!d_weights) return fail(XENG_ERR_ARG, "null pointer");
+  if (nbeam <= 0 || nframe > 65535) return fail(XENG_ERR_ARG, "bad sizes");
+  XENG_CUDA(xeng::launch_upchan_beamform(static_cast<const uint8_t*>(d_in), static_cast<const float2*>(d_weights),
+                                         static_cast<float2*>(d_out), nframe, nfine, nchan, ninput, nbeam,
+                                         static_cast<cudaStream_t>(stream)));
+  return XENG_OK;
+}
+
 // ------------------------------------------------------------------------------------ Beamform
 int xeng_bf_create(xeng_bf_t* out, int gpu, int ninput, int nchan, int ntime, int nbeam, int ntime_blocks) {
   if (!out) return fail(XENG_ERR_ARG, "null handle pointer");

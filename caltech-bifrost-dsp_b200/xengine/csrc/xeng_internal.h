@@ -61,4 +61,10 @@ cudaError_t launch_vlbi_tap(const float2* in, float2* out, int nchan, int nbeam,
 cudaError_t launch_beam_integrate(const float2* in, float* out, int nchan, int nbeam, int ntime, int ntime_sum,
                                   int beam0, int nbeam_out, cudaStream_t stream);
 
+// offline upchannelise path (xeng_upchan.cu)
+cudaError_t launch_upchan_fft(const uint8_t* in, float2* out, long nframe, int nfine, int nchan, int ninput, int layout,
+                              cudaStream_t stream);
+cudaError_t launch_upchan_beamform(const uint8_t* in, const float2* w, float2* out, long nframe, int nfine, int nchan,
+                                   int ninput, int nbeam, cudaStream_t stream);
+
 }  // namespace xeng

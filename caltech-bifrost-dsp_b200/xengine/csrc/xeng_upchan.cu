@@ -1,0 +1,261 @@
+// Offline upchannelise path: a short FFT along blocks of consecutive time samples of the raw 4+4-bit
+// voltages, then either the upchannelised voltages themselves or the offline beamformer's weighted sum over inputs.
+//
+// In the reference this is a chain of stock bifrost blocks working through HBM-sized intermediates
+// (/root/reference/pipeline/scripts/lwa352-upchan-bf.py:94-113 and lwa352-upchan-imag.py:93-98):
+//   TrigBufSourceBlock  ci4 [time][fine_time][freq][stand][pol]        (trigger_source_block.py:37-41)
+//   blocks.transpose -> [time][freq][stand][pol][fine_time]
+//   blocks.fft(axes='fine_time')  -> cf32 [time][freq][stand][pol][fine_freq]   (forward, unnormalised, no fftshift)
+//   imag:  blocks.transpose -> [time][freq][fine_freq][stand][pol], merge (freq, fine_freq)
+//   bf:    BfOfflineWeightsBlock: x *= cal * coeffs, coeffs [beam][freq][stand][pol][fine_freq]
+//          (beamform_offline_block.py:218-240), blocks.reduce over stand, then over pol
+//          -> cf32 [time][beam][freq][fine_freq]
+// Here each is ONE kernel: a thread transforms one (frame, chan, input) series in registers (radix-2 DIF, compile-time
+// unrolled, twiddles as immediates), so the transposes never exist and, for the beamformer, neither do the
+// upchannelised voltages (8 B per sample) nor the per-beam weighted copy of them (8 B per sample per beam).
+// Algorithmic bytes: fft  1 B read + 8 B written per sample;  beamform  1 B read per sample + weights once
+// (8 B * nbeam * nchan * ninput * nfine) + 8 B * nbeam / ninput per sample written.  Both HBM-bound.
+#include "xeng_internal.h"
+
+namespace xeng {
+namespace {
+
+// cos / sin of 2*pi*t/32, t = 0..15 (a switch over a compile-time t folds to an immediate)
+__device__ __forceinline__ float tw_cos(int t) {
+  switch (t) {
+    case 0: return 1.0f;
+    case 1: return 0.98078528040323043f;
+    case 2: return 0.92387953251128674f;
+    case 3: return 0.83146961230254524f;
+    case 4: return 0.70710678118654757f;
+    case 5: return 0.55557023301960229f;
+    case 6: return 0.38268343236508984f;
+    case 7: return 0.19509032201612833f;
+    case 8: return 0.0f;
+    case 9: return -0.19509032201612833f;
+    case 10: return -0.38268343236508984f;
+    case 11: return -0.55557023301960229f;
+    case 12: return -0.70710678118654757f;
+    case 13: return -0.83146961230254524f;
+    case 14: return -0.92387953251128674f;
+    default: return -0.98078528040323043f;
+  }
+}
+__device__ __forceinline__ float tw_sin(int t) { return t <= 8 ? tw_cos(8 - t) : tw_cos(t - 8); }
+
+__host__ __device__ constexpr int bitrev(int v, int n) {
+  int r = 0;
+  for (int b = 1; b < n; b <<= 1) { r = (r << 1) | (v & 1); v >>= 1; }
+  return r;
+}
+
+// Forward DFT X[k] = sum_n x[n] exp(-2 pi i n k / N) in place, decimation in frequency: element j of the result
+// holds X[bitrev(j)].
+template <int N>
+__device__ __forceinline__ void fft_dif(float (&re)[N], float (&im)[N]) {
+#pragma unroll
+  for (int half = N / 2; half >= 1; half >>= 1) {
+#pragma unroll
+    for (int base = 0; base < N; base += 2 * half) {
+#pragma unroll
+      for (int j = 0; j < half; ++j) {
+        const int a = base + j, b = a + half;
+        const float dr = re[a] - re[b], di = im[a] - im[b];
+        re[a] += re[b];
+        im[a] += im[b];
+        const int t = j * (16 / half);   // twiddle exp(-2 pi i t / 32)
+        if (t == 0) {
+          re[b] = dr; im[b] = di;
+        } else if (t == 8) {             // times -i
+          re[b] = di; im[b] = -dr;
+        } else {
+          const float c = tw_cos(t), s = tw_sin(t);
+          re[b] = dr * c + di * s;
+          im[b] = di * c - dr * s;
+        }
+      }
+    }
+  }
+}
+
+// 4+4-bit complex byte -> (re, im), the unpack every block of the path uses (corr_block.py:270-275)
+__device__ __forceinline__ void unpack4(uint32_t b, float& r, float& i) {
+  r = static_cast<float>(static_cast<int>(static_cast<int8_t>(b)) >> 4);
+  i = static_cast<float>(static_cast<int>(static_cast<int8_t>(b << 4)) >> 4);
+}
+
+// Loads the N samples of series (frame, chan, input) and transforms them.  in: u8 [nframe][N][nchan][ninput].
+template <int N>
+__device__ __forceinline__ void load_fft(const uint8_t* __restrict__ in, long frame, int chan, int input, int nchan,
+                                         int ninput, float (&re)[N], float (&im)[N]) {
+  const uint8_t* p = in + ((frame * N) * nchan + chan) * static_cast<long>(ninput) + input;
+  const long step = static_cast<long>(nchan) * ninput;
+  uint32_t raw[N];
+#pragma unroll
+  for (int n = 0; n < N; ++n) raw[n] = __ldg(p + n * step);
+#pragma unroll
+  for (int n = 0; n < N; ++n) unpack4(raw[n], re[n], im[n]);
+  fft_dif<N>(re, im);
+}
+
+constexpr int UPCHAN_WARPS = 4;
+constexpr int TILE_F2 = 32 * 32 + 32;   // a warp's 32 inputs x N bins as float2, one pad element per 32
+
+// flat element f = input_in_warp * N + k of a warp's tile; one pad per 32 keeps both access patterns conflict-free
+__device__ __forceinline__ int tile_idx(int f) { return f + (f >> 5); }
+
+// grid (nframe * nchan, ceil(ninput / 128)), 128 threads; lane = input.
+// layout 0: out cf32 [nframe][nchan][ninput][N]   (bf script order)   -- through a per-warp shared-memory transpose
+// layout 1: out cf32 [nframe][nchan][N][ninput]   (imag script order, = merged freq axis [nchan * N])
+template <int N>
+__global__ void __launch_bounds__(UPCHAN_WARPS * 32) upchan_fft_kernel(const uint8_t* __restrict__ in,
+                                                                       float2* __restrict__ out, int nchan, int ninput,
+                                                                       int layout) {
+  __shared__ float2 tile[UPCHAN_WARPS][TILE_F2];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long row = blockIdx.x;   // frame * nchan + chan
+  const long frame = row / nchan;
+  const int chan = static_cast<int>(row - frame * nchan);
+  const int i0 = (blockIdx.y * UPCHAN_WARPS + warp) * 32;
+  if (i0 >= ninput) return;
+  const int nv = min(32, ninput - i0);
+  float re[N], im[N];
+  if (lane < nv) load_fft<N>(in, frame, chan, i0 + lane, nchan, ninput, re, im);
+  if (layout == 1) {
+    if (lane < nv) {
+      float2* o = out + (row * N) * ninput + i0 + lane;
+#pragma unroll
+      for (int j = 0; j < N; ++j) __stcs(o + static_cast<long>(bitrev(j, N)) * ninput, make_float2(re[j], im[j]));
+    }
+    return;
+  }
+  if (lane < nv) {
+#pragma unroll
+    for (int j = 0; j < N; ++j) tile[warp][tile_idx(lane * N + bitrev(j, N))] = make_float2(re[j], im[j]);
+  }
+  __syncwarp();
+  float2* o = out + (row * ninput + i0) * N;   // the warp's nv * N outputs are contiguous
+#pragma unroll
+  for (int j = 0; j < N; ++j) {
+    const int f = j * 32 + lane;
+    if (f < nv * N) __stcs(o + f, tile[warp][tile_idx(f)]);
+  }
+}
+
+constexpr int BF_BC = 4;   // beams per pass over the inputs
+
+// grid (nchan, nframe), 128 threads.  Each warp walks blocks of 32 inputs: lane = input for the transform, then the
+// tile is re-read with lane = (input group g, bin k) so the weight rows w[beam][chan][input][0..N) are read as
+// contiguous 8*N-byte runs, and every lane keeps BF_BC running sums.  Warps and input groups are reduced at the end.
+// w: cf32 [nbeam][nchan][ninput][N];  out: cf32 [nframe][nbeam][nchan][N].
+template <int N>
+__global__ void __launch_bounds__(UPCHAN_WARPS * 32) upchan_beamform_kernel(const uint8_t* __restrict__ in,
+                                                                            const float2* __restrict__ w,
+                                                                            float2* __restrict__ out, int nchan,
+                                                                            int ninput, int nbeam) {
+  __shared__ float2 tile[UPCHAN_WARPS][TILE_F2];
+  __shared__ float2 red[UPCHAN_WARPS][BF_BC][32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int chan = blockIdx.x;
+  const long frame = blockIdx.y;
+  const int nblk = (ninput + 31) >> 5;
+  for (int b0 = 0; b0 < nbeam; b0 += BF_BC) {
+    float2 acc[BF_BC];
+#pragma unroll
+    for (int b = 0; b < BF_BC; ++b) acc[b] = make_float2(0.f, 0.f);
+    for (int blk = warp; blk < nblk; blk += UPCHAN_WARPS) {
+      const int i0 = blk * 32;
+      const int nv = min(32, ninput - i0);
+      __syncwarp();
+      if (lane < nv) {
+        float re[N], im[N];
+        load_fft<N>(in, frame, chan, i0 + lane, nchan, ninput, re, im);
+#pragma unroll
+        for (int j = 0; j < N; ++j) tile[warp][tile_idx(lane * N + bitrev(j, N))] = make_float2(re[j], im[j]);
+      }
+      __syncwarp();
+      const float2* wrow = w + (static_cast<long>(b0) * nchan + chan) * ninput * N + static_cast<long>(i0) * N;
+      const long wbeam = static_cast<long>(nchan) * ninput * N;
+#pragma unroll 4
+      for (int j = 0; j < N; ++j) {
+        const int f = j * 32 + lane;   // = input_in_block * N + k
+        if (f < nv * N) {
+          const float2 x = tile[warp][tile_idx(f)];
+#pragma unroll
+          for (int b = 0; b < BF_BC; ++b) {
+            if (b0 + b < nbeam) {
+              const float2 c = __ldg(wrow + b * wbeam + f);
+              acc[b].x += c.x * x.x - c.y * x.y;
+              acc[b].y += c.x * x.y + c.y * x.x;
+            }
+          }
+        }
+      }
+    }
+    // lanes sharing a bin k (lane % N) hold different input groups: fold them
+#pragma unroll
+    for (int b = 0; b < BF_BC; ++b) {
+#pragma unroll
+      for (int off = 16; off >= N; off >>= 1) {
+        acc[b].x += __shfl_xor_sync(0xffffffffu, acc[b].x, off);
+        acc[b].y += __shfl_xor_sync(0xffffffffu, acc[b].y, off);
+      }
+      red[warp][b][lane] = acc[b];
+    }
+    __syncthreads();
+    if (threadIdx.x < BF_BC * N) {
+      const int b = threadIdx.x / N, k = threadIdx.x - b * N;
+      if (b0 + b < nbeam) {
+        float2 s = red[0][b][k];
+#pragma unroll
+        for (int q = 1; q < UPCHAN_WARPS; ++q) { s.x += red[q][b][k].x; s.y += red[q][b][k].y; }
+        out[((frame * nbeam + b0 + b) * nchan + chan) * N + k] = s;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+template <int N>
+cudaError_t fft_n(const uint8_t* in, float2* out, long nframe, int nchan, int ninput, int layout, cudaStream_t st) {
+  dim3 grid(static_cast<unsigned>(nframe * nchan), (ninput + UPCHAN_WARPS * 32 - 1) / (UPCHAN_WARPS * 32));
+  upchan_fft_kernel<N><<<grid, UPCHAN_WARPS * 32, 0, st>>>(in, out, nchan, ninput, layout);
+  return cudaGetLastError();
+}
+template <int N>
+cudaError_t bf_n(const uint8_t* in, const float2* w, float2* out, long nframe, int nchan, int ninput, int nbeam,
+                 cudaStream_t st) {
+  dim3 grid(nchan, static_cast<unsigned>(nframe));
+  upchan_beamform_kernel<N><<<grid, UPCHAN_WARPS * 32, 0, st>>>(in, w, out, nchan, ninput, nbeam);
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t launch_upchan_fft(const uint8_t* in, float2* out, long nframe, int nfine, int nchan, int ninput, int layout,
+                              cudaStream_t st) {
+  if (nframe <= 0) return cudaSuccess;
+  switch (nfine) {
+    case 2: return fft_n<2>(in, out, nframe, nchan, ninput, layout, st);
+    case 4: return fft_n<4>(in, out, nframe, nchan, ninput, layout, st);
+    case 8: return fft_n<8>(in, out, nframe, nchan, ninput, layout, st);
+    case 16: return fft_n<16>(in, out, nframe, nchan, ninput, layout, st);
+    case 32: return fft_n<32>(in, out, nframe, nchan, ninput, layout, st);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+cudaError_t launch_upchan_beamform(const uint8_t* in, const float2* w, float2* out, long nframe, int nfine, int nchan,
+                                   int ninput, int nbeam, cudaStream_t st) {
+  if (nframe <= 0) return cudaSuccess;
+  switch (nfine) {
+    case 2: return bf_n<2>(in, w, out, nframe, nchan, ninput, nbeam, st);
+    case 4: return bf_n<4>(in, w, out, nframe, nchan, ninput, nbeam, st);
+    case 8: return bf_n<8>(in, w, out, nframe, nchan, ninput, nbeam, st);
+    case 16: return bf_n<16>(in, w, out, nframe, nchan, ninput, nbeam, st);
+    case 32: return bf_n<32>(in, w, out, nframe, nchan, ninput, nbeam, st);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+}  // namespace xeng

@@ -118,6 +118,24 @@ def snap2_assemble(d_pkts, npkt, pkt_stride, d_out, seq0, ntime, nchan, ninput, 
                                           ptr(d_nvalid), ptr(stream)), "xeng_snap2_assemble")
 
 
+UPCHAN_FINE_LAST, UPCHAN_FREQ_MERGED = 0, 1
+
+
+def upchan_fft(d_in, d_out, nframe, nfine, nchan, ninput, layout=UPCHAN_FINE_LAST, stream=None):
+    """transpose -> fft(axes='fine_time') [-> transpose] of the offline scripts as one kernel
+    (lwa352-upchan-bf.py:94-96, lwa352-upchan-imag.py:93-98).  d_in u8 [nframe][nfine][nchan][ninput];
+    d_out cf32 [nframe][nchan][ninput][nfine] (FINE_LAST) or [nframe][nchan][nfine][ninput] (FREQ_MERGED)."""
+    check(_lib.load().xeng_upchan_fft(ptr(d_in), ptr(d_out), int(nframe), int(nfine), int(nchan), int(ninput),
+                                      int(layout), ptr(stream)), "xeng_upchan_fft")
+
+
+def upchan_beamform(d_in, d_weights, d_out, nframe, nfine, nchan, ninput, nbeam, stream=None):
+    """lwa352-upchan-bf.py:94-113 (upchannelise, BfOfflineWeightsBlock's multiply, reduce over stand and pol) as
+    one kernel.  d_weights cf32 [nbeam][nchan][ninput][nfine]; d_out cf32 [nframe][nbeam][nchan][nfine]."""
+    check(_lib.load().xeng_upchan_beamform(ptr(d_in), ptr(d_weights), ptr(d_out), int(nframe), int(nfine), int(nchan),
+                                           int(ninput), int(nbeam), ptr(stream)), "xeng_upchan_beamform")
+
+
 def subsel_packets(d_in, d_out, d_vismap, d_conj, nvis, nchan, nchan_sum, wpc, layout=PAYLOAD_PY, stream=None):
     """bfXgpuSubSelect written in CorrOutputPart's packet order (corr_output_part_block.py:378-391, 429-463):
     COR = int32 [nvis/4][nchan/nchan_sum][4][2]; PY = big-endian int32 [nvis][nchan/nchan_sum][2]."""

@@ -126,6 +126,24 @@ int xeng_reorder_packets(const void* d_in, void* d_out, const void* d_a2bl, cons
 int xeng_snap2_assemble(const void* d_pkts, int npkt, int64_t pkt_stride, void* d_out, uint64_t seq0, int ntime,
                         int nchan, int ninput, int first_chan, int zero_first, void* d_nvalid, void* cuda_stream);
 
+/* ------------------------------------------------------------------ offline upchannelise */
+/* Replaces the stock bifrost chain transpose -> fft(axes='fine_time') [-> transpose] of the offline scripts
+ * (scripts/lwa352-upchan-bf.py:94-96, scripts/lwa352-upchan-imag.py:93-98) with one kernel.
+ * d_in u8 [nframe][nfine][nchan][ninput] (TrigBufSourceBlock's ci4 [time][fine_time][freq][stand][pol],
+ * trigger_source_block.py:37-41); forward unnormalised DFT along fine_time, nfine in {2,4,8,16,32}, bins in natural
+ * order (no fftshift).  d_out cf32: XENG_UPCHAN_FINE_LAST [nframe][nchan][ninput][nfine] (bf script),
+ * XENG_UPCHAN_FREQ_MERGED [nframe][nchan][nfine][ninput] = [nframe][nchan*nfine][stand][pol] (imag script). */
+#define XENG_UPCHAN_FINE_LAST 0
+#define XENG_UPCHAN_FREQ_MERGED 1
+int xeng_upchan_fft(const void* d_in, void* d_out, int nframe, int nfine, int nchan, int ninput, int layout,
+                    void* cuda_stream);
+/* The whole of lwa352-upchan-bf.py:94-113 in one kernel: upchannelise, multiply by the per-(beam, chan, input, bin)
+ * weights BfOfflineWeightsBlock applies (beamform_offline_block.py:218-240: calibration x geometric coefficients,
+ * constant over a gulp) and reduce over stand and pol.  d_weights cf32 [nbeam][nchan][ninput][nfine];
+ * d_out cf32 [nframe][nbeam][nchan][nfine]. */
+int xeng_upchan_beamform(const void* d_in, const void* d_weights, void* d_out, int nframe, int nfine, int nchan,
+                         int ninput, int nbeam, void* cuda_stream);
+
 /* ------------------------------------------------------------------ Beamform / BeamformSum */
 typedef struct xeng_bf_s* xeng_bf_t;
 

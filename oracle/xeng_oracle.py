@@ -370,3 +370,43 @@ def beam_power_sum_single(x, ntime_sum, beam_id):
     """bfBeamformIntegrateSingleBeam (beamform_sum_single_beam_block.py:114):
     the dual-pol beam ``beam_id`` only -> [ntime//ntime_sum, nchan, 4]."""
     return beam_power_sum(x[:, 2 * beam_id : 2 * beam_id + 2, :], ntime_sum)[0]
+
+
+# ---------------------------------------------------------------------------
+# Offline upchannelise path (SURVEY 8 f4)
+# ---------------------------------------------------------------------------
+
+def upchannelize(v_u8, layout="fine_last"):
+    """pipeline/scripts/lwa352-upchan-bf.py:94-96: TrigBufSourceBlock's ci4 [time][fine_time][freq][stand][pol]
+    (trigger_source_block.py:37-41) is transposed to fine_time-last and Fourier transformed along fine_time by
+    bifrost's fft block (forward, unnormalised, no fftshift -- stock bifrost, absent here; numpy's fft has the same
+    definition).  v_u8: uint8 [nframe, nfine, nchan, ninput].  Returns complex128 [nframe, nchan, ninput, nfine]
+    ("fine_last") or, as lwa352-upchan-imag.py:93-98 transposes it, [nframe, nchan, nfine, ninput]
+    ("freq_merged")."""
+    r, i = unpack4(v_u8)
+    x = (r.astype(np.float64) + 1j * i.astype(np.float64)).transpose(0, 2, 3, 1)
+    X = np.fft.fft(x, axis=-1)
+    if layout == "freq_merged":
+        X = X.transpose(0, 1, 3, 2)
+    return np.ascontiguousarray(X)
+
+
+def upchan_beamform(v_u8, weights):
+    """lwa352-upchan-bf.py:94-113: upchannelise, multiply by cal * coeffs
+    (beamform_offline_block.py:218-240; both [beam][chan][stand][pol][fine], constant over a gulp), reduce over
+    stand then pol.  weights complex [nbeam, nchan, ninput, nfine].
+    Returns complex128 [nframe, nbeam, nchan, nfine]."""
+    X = upchannelize(v_u8)
+    return np.einsum("bcik,fcik->fbck", np.asarray(weights).astype(np.complex128), X, optimize=True)
+
+
+def offline_beam_weights(freqs, delays_ns, weighting=None):
+    """BfOfflineWeightsBlock.compute_weights, the part after the astropy pointing
+    (beamform_offline_block.py:126-134): delays are made relative to the largest one, scaled by the per-input
+    antenna weighting, and turned into phases at every fine frequency.  freqs [nchan * nfine] in Hz, delays_ns
+    [ninput].  Returns complex [nchan * nfine, ninput]."""
+    d = np.asarray(delays_ns, dtype=np.float64)
+    d = d.max() - d
+    if weighting is not None:
+        d = np.asarray(weighting) * d
+    return np.exp(2j * np.pi * np.asarray(freqs, dtype=np.float64)[:, None] * d * 1e-9)
