@@ -9,3 +9,5 @@ from .beamform_block import Beamform  # noqa: F401
 from .beamform_sum_beams_block import BeamformSumBeams  # noqa: F401
 from .beamform_sum_block import BeamformSum  # noqa: F401
 from .beamform_sum_single_beam_block import BeamformSumSingleBeam  # noqa: F401
+from .beamform_output_block import BeamformOutput  # noqa: F401
+from .beamform_vlbi_output_block import BeamformVlbiOutput  # noqa: F401

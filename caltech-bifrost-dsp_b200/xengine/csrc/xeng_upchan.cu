@@ -143,73 +143,94 @@ __global__ void __launch_bounds__(UPCHAN_WARPS * 32) upchan_fft_kernel(const uin
 }
 
 constexpr int BF_BC = 4;   // beams per pass over the inputs
+constexpr int BF_FR = 5;   // frames per CTA = warps per CTA (a 480-sample gulp is 15 frames of 32)
 
-// grid (nchan, nframe), 128 threads.  Each warp walks blocks of 32 inputs: lane = input for the transform, then the
-// tile is re-read with lane = (input group g, bin k) so the weight rows w[beam][chan][input][0..N) are read as
-// contiguous 8*N-byte runs, and every lane keeps BF_BC running sums.  Warps and input groups are reduced at the end.
+// grid (nchan, ceil(nframe / BF_FR)), BF_FR warps.  The CTA walks blocks of 32 inputs.  Phase 1: warp q transforms
+// frame frame0 + q of the block (lane = input) into its shared-memory tile.  Phase 2: the warps split the block's
+// 32 * N (input, bin) elements; a lane loads the BF_BC weights of its element ONCE (contiguous 256-byte rows of
+// w[beam][chan][input][0..N)) and applies them to all BF_FR frames, so a weight is read nframe / BF_FR times in all
+// instead of nframe times.  Element f = input * N + k sits in lane f % 32, hence a lane always works on bin
+// k = lane % N and keeps BF_BC x BF_FR running sums; warps and the 32 / N input groups are folded at the end.
 // w: cf32 [nbeam][nchan][ninput][N];  out: cf32 [nframe][nbeam][nchan][N].
 template <int N>
-__global__ void __launch_bounds__(UPCHAN_WARPS * 32) upchan_beamform_kernel(const uint8_t* __restrict__ in,
-                                                                            const float2* __restrict__ w,
-                                                                            float2* __restrict__ out, int nchan,
-                                                                            int ninput, int nbeam) {
-  __shared__ float2 tile[UPCHAN_WARPS][TILE_F2];
-  __shared__ float2 red[UPCHAN_WARPS][BF_BC][32];
+__global__ void __launch_bounds__(BF_FR * 32) upchan_beamform_kernel(const uint8_t* __restrict__ in,
+                                                                     const float2* __restrict__ w,
+                                                                     float2* __restrict__ out, int nframe, int nchan,
+                                                                     int ninput, int nbeam) {
+  __shared__ float2 tile[BF_FR * TILE_F2];
+  float2* red = tile;   // [warp][BF_BC][BF_FR][32], aliased onto the tiles once a pass over the inputs is done
+  static_assert(BF_FR * BF_BC * BF_FR * 32 <= BF_FR * TILE_F2, "reduction scratch must fit in the tiles");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int chan = blockIdx.x;
-  const long frame = blockIdx.y;
+  const long frame0 = static_cast<long>(blockIdx.y) * BF_FR;
+  const bool valid = frame0 + warp < nframe;
   const int nblk = (ninput + 31) >> 5;
+  const long wbeam = static_cast<long>(nchan) * ninput * N;
   for (int b0 = 0; b0 < nbeam; b0 += BF_BC) {
-    float2 acc[BF_BC];
+    if (!valid)   // a frame past the end contributes zeros (its outputs are not written)
+      for (int i = lane; i < TILE_F2; i += 32) tile[warp * TILE_F2 + i] = make_float2(0.f, 0.f);
+    float2 acc[BF_BC][BF_FR];
 #pragma unroll
-    for (int b = 0; b < BF_BC; ++b) acc[b] = make_float2(0.f, 0.f);
-    for (int blk = warp; blk < nblk; blk += UPCHAN_WARPS) {
+    for (int b = 0; b < BF_BC; ++b)
+#pragma unroll
+      for (int q = 0; q < BF_FR; ++q) acc[b][q] = make_float2(0.f, 0.f);
+    for (int blk = 0; blk < nblk; ++blk) {
       const int i0 = blk * 32;
       const int nv = min(32, ninput - i0);
-      __syncwarp();
-      if (lane < nv) {
+      __syncthreads();   // phase 2 of the previous block has finished with the tiles
+      if (valid && lane < nv) {
         float re[N], im[N];
-        load_fft<N>(in, frame, chan, i0 + lane, nchan, ninput, re, im);
+        load_fft<N>(in, frame0 + warp, chan, i0 + lane, nchan, ninput, re, im);
 #pragma unroll
-        for (int j = 0; j < N; ++j) tile[warp][tile_idx(lane * N + bitrev(j, N))] = make_float2(re[j], im[j]);
+        for (int j = 0; j < N; ++j) tile[warp * TILE_F2 + tile_idx(lane * N + bitrev(j, N))] = make_float2(re[j], im[j]);
       }
-      __syncwarp();
+      __syncthreads();
       const float2* wrow = w + (static_cast<long>(b0) * nchan + chan) * ninput * N + static_cast<long>(i0) * N;
-      const long wbeam = static_cast<long>(nchan) * ninput * N;
-#pragma unroll 4
-      for (int j = 0; j < N; ++j) {
+      for (int j = warp; j < N; j += BF_FR) {
         const int f = j * 32 + lane;   // = input_in_block * N + k
         if (f < nv * N) {
-          const float2 x = tile[warp][tile_idx(f)];
+          float2 c[BF_BC];
 #pragma unroll
-          for (int b = 0; b < BF_BC; ++b) {
-            if (b0 + b < nbeam) {
-              const float2 c = __ldg(wrow + b * wbeam + f);
-              acc[b].x += c.x * x.x - c.y * x.y;
-              acc[b].y += c.x * x.y + c.y * x.x;
+          for (int b = 0; b < BF_BC; ++b) c[b] = (b0 + b < nbeam) ? __ldg(wrow + b * wbeam + f) : make_float2(0.f, 0.f);
+          const int ti = tile_idx(f);
+#pragma unroll
+          for (int q = 0; q < BF_FR; ++q) {
+            const float2 x = tile[q * TILE_F2 + ti];
+#pragma unroll
+            for (int b = 0; b < BF_BC; ++b) {
+              acc[b][q].x += c[b].x * x.x - c[b].y * x.y;
+              acc[b][q].y += c[b].x * x.y + c[b].y * x.x;
             }
           }
         }
       }
     }
-    // lanes sharing a bin k (lane % N) hold different input groups: fold them
+    __syncthreads();   // tiles are dead: reuse them as reduction scratch
 #pragma unroll
     for (int b = 0; b < BF_BC; ++b) {
 #pragma unroll
-      for (int off = 16; off >= N; off >>= 1) {
-        acc[b].x += __shfl_xor_sync(0xffffffffu, acc[b].x, off);
-        acc[b].y += __shfl_xor_sync(0xffffffffu, acc[b].y, off);
+      for (int q = 0; q < BF_FR; ++q) {
+        float2 a = acc[b][q];
+#pragma unroll
+        for (int off = 16; off >= N; off >>= 1) {   // lanes sharing bin k = lane % N hold different input groups
+          a.x += __shfl_xor_sync(0xffffffffu, a.x, off);
+          a.y += __shfl_xor_sync(0xffffffffu, a.y, off);
+        }
+        red[((warp * BF_BC + b) * BF_FR + q) * 32 + lane] = a;
       }
-      red[warp][b][lane] = acc[b];
     }
     __syncthreads();
-    if (threadIdx.x < BF_BC * N) {
-      const int b = threadIdx.x / N, k = threadIdx.x - b * N;
-      if (b0 + b < nbeam) {
-        float2 s = red[0][b][k];
+    for (int e = threadIdx.x; e < BF_BC * BF_FR * N; e += BF_FR * 32) {
+      const int k = e % N, q = (e / N) % BF_FR, b = e / (N * BF_FR);
+      if (b0 + b < nbeam && frame0 + q < nframe) {
+        float2 s = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int q = 1; q < UPCHAN_WARPS; ++q) { s.x += red[q][b][k].x; s.y += red[q][b][k].y; }
-        out[((frame * nbeam + b0 + b) * nchan + chan) * N + k] = s;
+        for (int wq = 0; wq < BF_FR; ++wq) {
+          const float2 r = red[((wq * BF_BC + b) * BF_FR + q) * 32 + k];
+          s.x += r.x;
+          s.y += r.y;
+        }
+        out[(((frame0 + q) * nbeam + b0 + b) * nchan + chan) * N + k] = s;
       }
     }
     __syncthreads();
@@ -225,8 +246,8 @@ cudaError_t fft_n(const uint8_t* in, float2* out, long nframe, int nchan, int ni
 template <int N>
 cudaError_t bf_n(const uint8_t* in, const float2* w, float2* out, long nframe, int nchan, int ninput, int nbeam,
                  cudaStream_t st) {
-  dim3 grid(nchan, static_cast<unsigned>(nframe));
-  upchan_beamform_kernel<N><<<grid, UPCHAN_WARPS * 32, 0, st>>>(in, w, out, nchan, ninput, nbeam);
+  dim3 grid(nchan, static_cast<unsigned>((nframe + BF_FR - 1) / BF_FR));
+  upchan_beamform_kernel<N><<<grid, BF_FR * 32, 0, st>>>(in, w, out, static_cast<int>(nframe), nchan, ninput, nbeam);
   return cudaGetLastError();
 }
 

@@ -20,3 +20,8 @@ timeout 600 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__byte
     --log-file gpurun_out/${TAG}_path_kernels.csv python scripts/prof_path.py > gpurun_out/${TAG}_ncu3.log 2>&1; echo "ncu path rc=$?"
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:beamform_kernel -s 2 -c 1 \
     -f -o gpurun_out/${TAG}_beam python scripts/prof_beam.py > gpurun_out/${TAG}_ncu4.log 2>&1; echo "ncu beam rc=$?"
+# offline upchannelise kernels: duration + DRAM bytes per launch
+timeout 300 python scripts/prof_upchan.py > gpurun_out/${TAG}_upchan_plain.log 2>&1 && \
+timeout 600 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,lts__t_bytes.sum,sm__warps_active.avg.pct_of_peak_sustained_active --clock-control none \
+    -k regex:"upchan_" -c 12 --csv \
+    --log-file gpurun_out/${TAG}_upchan_kernels.csv python scripts/prof_upchan.py > gpurun_out/${TAG}_ncu5.log 2>&1; echo "ncu upchan rc=$?"

@@ -470,3 +470,54 @@ def test_beamform_sum_blocks_headers_and_sizes(host_only):
     assert [len(s) for s in spans] == [og2]
     with pytest.raises(AssertionError):
         BeamformSumBeams(LOG, iring, oring, nchan=NCHAN, ntime_gulp=10, ntime_sum=4)
+
+
+def test_beamform_output_packets_and_destinations(host_only):
+    """BeamformOutput host logic (beamform_output_block.py:243-245,311-317,353-361): destinations assigned to beams
+    round-robin from the command lists, one packet per (beam, time step) carrying the contiguous [nchan][4] row, the
+    header bytes of send_packets_python, seq advancing by ntime_gulp * navg per packet, beams at 0.0.0.0 skipped."""
+    import struct
+    from xengine.blocks import BeamformOutput
+    nt, nbeam = 3, 4
+    pw = np.arange(nbeam * nt * NCHAN * 4, dtype=np.float32)
+    ring = ringshim.Ring("bf-pow")
+    hdr = bf_header(nbeam, acc_len=24)
+    hdr.update({'npol': 2, 'chan0': 96, 'seq0': 480})
+    fill(ring, [(hdr, [pw, pw[:8]])])                                     # second span is short: skipped
+    blk = BeamformOutput(LOG, ring, guarantee=False, ntime_gulp=nt, pipeline_idx=3, nchan=NCHAN, nbeam=nbeam)
+    pkts = []
+    blk.sink = lambda b, h, p: pkts.append((b, h, p))
+    blk.process_command_strings(cmd({"dest_ip": ["10.0.0.1", "0.0.0.0"], "dest_port": [10000, 10001, 10002]}))
+    blk.main()
+    assert blk.beam_ips == ["10.0.0.1", "0.0.0.0", "10.0.0.1", "0.0.0.0"] and blk.beam_ports == [10000, 10001, 10002, 10000]
+    assert [p[0] for p in pkts] == [0] * nt + [2] * nt                    # beams 1 and 3 have no destination
+    rows = pw.reshape(nbeam, nt, NCHAN * 4)
+    for k, (b, h, p) in enumerate(pkts):
+        t = k % nt
+        assert struct.unpack(">6B2HQ", h) == (2, b, 1, NCHAN, nbeam, 32, 24, 96, 480 + t * nt * 24)
+        assert np.array_equal(np.frombuffer(p, dtype=np.float32), rows[b, t])
+
+
+def test_beamform_vlbi_output_rows(host_only):
+    """BeamformVlbiOutput host logic (beamform_vlbi_output_block.py:228,260-262): span cf32 [nchan][nbeam][ntime];
+    the first two single-pol beams go out as one [nchan][2] row per time sample, seq = seq0 + sample index; nothing
+    is sent while dest_ip is 0.0.0.0."""
+    from xengine.blocks import BeamformVlbiOutput
+    nt, nbeam = 40, 4
+    rng = np.random.default_rng(5)
+    volt = (rng.standard_normal((NCHAN, nbeam, nt)) + 1j * rng.standard_normal((NCHAN, nbeam, nt))).astype(np.complex64)
+    for ip, nexp in (("0.0.0.0", 0), ("10.0.0.9", 2 * nt)):
+        ring = ringshim.Ring("bf-volt")
+        vh = bf_header(nbeam)
+        vh['seq0'] = 1000
+        fill(ring, [(vh, [volt, volt * 2])])
+        blk = BeamformVlbiOutput(LOG, ring, guarantee=False, ntime_gulp=nt, pipeline_idx=1)
+        rows = []
+        blk.sink = lambda seq, p: rows.append((seq, np.frombuffer(p, dtype=np.complex64)))
+        blk.process_command_strings(cmd({"dest_ip": ip}))
+        blk.main()
+        assert len(rows) == nexp
+        for k, (seq, r) in enumerate(rows):
+            g, t = divmod(k, nt)
+            assert seq == 1000 + k
+            assert np.array_equal(r.reshape(NCHAN, 2), (volt * (g + 1))[:, 0:2, t])

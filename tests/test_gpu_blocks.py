@@ -334,3 +334,53 @@ def test_beamformer_graph_matches_oracle(torch_cuda):
         want_p = orc.beam_power_sum(want_v, ntime_sum)
         got_p = pspans[g].view(np.float32).reshape(nbeam // 2, nt // ntime_sum, nchan, 4)
         assert np.abs(got_p - want_p).max() / np.abs(want_p).max() <= 1e-5
+
+
+def test_beam_output_blocks_on_the_beamformer_graph(torch_cuda):
+    """Beamform -> {BeamformVlbiOutput (device span through xeng_bf_vlbi_tap), BeamformSumBeams -> BeamformOutput}:
+    the VLBI rows are the first two voltage beams of the oracle in [time][chan][beam] order
+    (beamform_vlbi_output_block.py:260-262) and every power packet is the oracle's [chan][4] row of its (beam, time
+    step) (beamform_output_block.py:353-359)."""
+    from xengine import ringshim
+    from xengine import runtime as rt
+    from xengine.blocks import Beamform, BeamformOutput, BeamformSumBeams, BeamformVlbiOutput
+    nstand, npol, nchan, nt, nbeam, ntime_sum, ngulp = 24, 2, 8, 96, 6, 24, 2
+    ninput = nstand * npol
+    rng = np.random.default_rng(77)
+    v = rng.integers(0, 256, size=(ngulp, nt, nchan, ninput), dtype=np.uint8)
+    hdr = header(nchan, nstand, npol)
+    r_in = ringshim.Ring("gpu-input", space="cuda")
+    r_bf = ringshim.Ring("bf-output", space="cuda")
+    r_pow = ringshim.Ring("bf-pow-output", space="cuda_host")
+    bf = Beamform(LOG, r_in, r_bf, nchan=nchan, nbeam=nbeam, ninput=ninput, ntime_gulp=nt, gpu=0)
+    w = (rng.standard_normal((nchan, nbeam, ninput)) + 1j * rng.standard_normal((nchan, nbeam, ninput))).astype(np.complex64)
+    bf.gains_cpu[...] = w
+    rt.copy_array(bf.gains_gpu, bf.gains_cpu)          # what Beamform.main does when a load time passes
+    bfs = BeamformSumBeams(LOG, r_bf, r_pow, nchan=nchan, ntime_gulp=nt, ntime_sum=ntime_sum, gpu=0)
+    vlbi = BeamformVlbiOutput(LOG, r_bf, ntime_gulp=nt)
+    pout = BeamformOutput(LOG, r_pow, ntime_gulp=nt // ntime_sum, pipeline_idx=2, nchan=nchan, nbeam=nbeam // 2)
+    rows, pkts = [], []
+    vlbi.sink = lambda seq, p: rows.append((seq, np.frombuffer(p, dtype=np.complex64).copy()))
+    pout.sink = lambda b, h, p: pkts.append((b, h, np.frombuffer(p, dtype=np.float32).copy()))
+    vlbi.process_command_strings(json.dumps({"id": "1", "cmd": "update", "val": {"kwargs": {"dest_ip": "10.1.1.1"}}}))
+    pout.process_command_strings(json.dumps({"id": "1", "cmd": "update", "val": {"kwargs": {"dest_ip": ["10.1.1.2"]}}}))
+    run_all([source(r_in, hdr, list(v)), threading.Thread(target=bf.main, name="Beamform"),
+             threading.Thread(target=bfs.main, name="BeamformSumBeams"),
+             threading.Thread(target=vlbi.main, name="BeamformVlbiOutput"),
+             threading.Thread(target=pout.main, name="BeamformOutput")])
+    assert len(rows) == ngulp * nt and len(pkts) == ngulp * (nbeam // 2) * (nt // ntime_sum)
+    k = 0
+    for g in range(ngulp):
+        want_v = orc.beamform(v[g], bf.gains_cpu)                       # [chan][beam][time]
+        for t in range(nt):
+            seq, r = rows[g * nt + t]
+            assert seq == g * nt + t
+            ref = want_v[:, 0:2, t]
+            assert np.abs(r.reshape(nchan, 2) - ref).max() / np.abs(want_v).max() <= 1e-5
+        want_p = orc.beam_power_sum(want_v, ntime_sum)                  # [beam/2][T][chan][4]
+        for b in range(nbeam // 2):
+            for T in range(nt // ntime_sum):
+                pb, _, p = pkts[k]
+                k += 1
+                assert pb == b
+                assert np.abs(p.reshape(nchan, 4) - want_p[b, T]).max() / np.abs(want_p).max() <= 1e-5

@@ -63,12 +63,13 @@ def test_upchan_fft_tone_lands_in_one_bin(torch_cuda):
     assert np.abs(got[..., 1:]).max() == 0.0
 
 
-@pytest.mark.parametrize("nfine,nbeam,ninput", [(32, 1, 704), (32, 4, 704), (32, 6, 100), (16, 3, 704), (2, 5, 96)])
-def test_upchan_beamform_matches_oracle(torch_cuda, nfine, nbeam, ninput):
+@pytest.mark.parametrize("nfine,nbeam,ninput,nframe", [(32, 1, 704, 4), (32, 4, 704, 7), (32, 6, 100, 5), (16, 3, 704, 11),
+                                                       (8, 2, 704, 1), (4, 9, 40, 6), (2, 5, 96, 4)])
+def test_upchan_beamform_matches_oracle(torch_cuda, nfine, nbeam, ninput, nframe):
     torch = torch_cuda
     from xengine import ops
     rng = np.random.default_rng(nfine + 10 * nbeam + ninput)
-    nframe, nchan = 4, 3
+    nchan = 3
     v = _edge_bytes(rng.integers(0, 256, size=(nframe, nfine, nchan, ninput), dtype=np.uint8))
     # weights built the way BfOfflineWeightsBlock does: cal gains x geometric phases (beamform_offline_block.py:126-134,218)
     freqs = 50e6 + np.arange(nchan * nfine) * (23925.78125 / nfine)

@@ -180,3 +180,26 @@ def test_snap2_packet_and_assembly_oracle():
     assert ngood == len(pkts) - 1 and not out[0, :ncp, :npp].any() and np.array_equal(out[1:], v[1:])
     out, ngood = orc.snap2_assemble(pkts, 51, 2, nchan, ninput, first_chan=100)     # a later, shorter window
     assert ngood == 2 * (nchan // ncp) * (ninput // npp) and np.array_equal(out, v[1:3])
+
+
+def test_upchannelize_oracle_against_literal_dft():
+    """The f4 oracle (numpy fft) against the textbook sum X[k] = sum_n x[n] exp(-2 pi i n k / N) the reference's
+    bifrost fft block computes (lwa352-upchan-bf.py:96: forward, unnormalised, no shift), both layouts; the N = 2
+    case is exactly (x0 + x1, x0 - x1); the weighted sum is linear in the weights."""
+    rng = np.random.default_rng(11)
+    for nfine in (2, 8, 32):
+        v = rng.integers(0, 256, size=(2, nfine, 3, 6), dtype=np.uint8)
+        r, i = orc.unpack4(v)
+        x = r.astype(np.float64) + 1j * i.astype(np.float64)              # [frame][n][chan][input]
+        n = np.arange(nfine)
+        lit = np.einsum("kn,fnci->fcik", np.exp(-2j * np.pi * np.outer(n, n) / nfine), x)
+        got = orc.upchannelize(v)
+        assert got.shape == (2, 3, 6, nfine) and np.allclose(got, lit, atol=1e-9)
+        assert np.array_equal(orc.upchannelize(v, "freq_merged"), got.transpose(0, 1, 3, 2))
+        if nfine == 2:
+            assert np.array_equal(got[..., 0], x[:, 0] + x[:, 1]) and np.array_equal(got[..., 1], x[:, 0] - x[:, 1])
+        w1 = rng.standard_normal((2, 3, 6, nfine)) + 1j * rng.standard_normal((2, 3, 6, nfine))
+        w2 = rng.standard_normal((2, 3, 6, nfine)) + 1j * rng.standard_normal((2, 3, 6, nfine))
+        assert np.allclose(orc.upchan_beamform(v, w1 + 2 * w2), orc.upchan_beamform(v, w1) + 2 * orc.upchan_beamform(v, w2))
+    w = orc.offline_beam_weights([50e6, 50.1e6], [0.0, 10.0, 4.0])
+    assert w.shape == (2, 3) and np.allclose(w[:, 1], 1.0) and np.isclose(w[0, 0], np.exp(2j * np.pi * 50e6 * 10e-9))
