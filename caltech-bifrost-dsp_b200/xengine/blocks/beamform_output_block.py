@@ -21,9 +21,10 @@ from .block_base import Block
 
 
 def pbeam_header(server, beam, tuning, nchan, nbeam, nserver, navg, chan0, seq):
-    """beamform_output_block.py:312-314."""
-    return np.array([server, beam, tuning, nchan, nbeam, nserver], dtype='>u1').tobytes() \
-        + np.array([navg, chan0], dtype='>u2').tobytes() + np.array([seq], dtype='>u8').tobytes()
+    """beamform_output_block.py:312-314.  The six leading fields are single bytes; values are taken modulo 256, as
+    the reference's np.array(..., dtype='>u1') did under the numpy it was written for."""
+    return np.array([int(x) & 0xFF for x in (server, beam, tuning, nchan, nbeam, nserver)], dtype='>u1').tobytes() \
+        + np.array([int(navg) & 0xFFFF, int(chan0) & 0xFFFF], dtype='>u2').tobytes() + np.array([seq], dtype='>u8').tobytes()
 
 
 class BeamformOutput(Block):

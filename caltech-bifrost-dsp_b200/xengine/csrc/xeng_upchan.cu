@@ -84,18 +84,35 @@ __device__ __forceinline__ void unpack4(uint32_t b, float& r, float& i) {
   i = static_cast<float>(static_cast<int>(static_cast<int8_t>(b << 4)) >> 4);
 }
 
-// Loads the N samples of series (frame, chan, input) and transforms them.  in: u8 [nframe][N][nchan][ninput].
+// Raw bytes of series (frame, chan, input), sample n in byte n % 4 of word n / 4.  in: u8 [nframe][N][nchan][ninput].
+template <int N>
+__device__ __forceinline__ void load_raw(const uint8_t* __restrict__ in, long frame, int chan, int input, int nchan,
+                                         int ninput, uint32_t (&raw)[(N + 3) / 4]) {
+  const uint8_t* p = in + ((frame * N) * nchan + chan) * static_cast<long>(ninput) + input;
+  const long step = static_cast<long>(nchan) * ninput;
+  uint32_t b[N];
+#pragma unroll
+  for (int n = 0; n < N; ++n) b[n] = __ldg(p + n * step);
+#pragma unroll
+  for (int q = 0; q < (N + 3) / 4; ++q) raw[q] = 0;
+#pragma unroll
+  for (int n = 0; n < N; ++n) raw[n >> 2] |= b[n] << (8 * (n & 3));
+}
+
+template <int N>
+__device__ __forceinline__ void fft_raw(const uint32_t (&raw)[(N + 3) / 4], float (&re)[N], float (&im)[N]) {
+#pragma unroll
+  for (int n = 0; n < N; ++n) unpack4(raw[n >> 2] >> (8 * (n & 3)), re[n], im[n]);
+  fft_dif<N>(re, im);
+}
+
+// Loads the N samples of series (frame, chan, input) and transforms them.
 template <int N>
 __device__ __forceinline__ void load_fft(const uint8_t* __restrict__ in, long frame, int chan, int input, int nchan,
                                          int ninput, float (&re)[N], float (&im)[N]) {
-  const uint8_t* p = in + ((frame * N) * nchan + chan) * static_cast<long>(ninput) + input;
-  const long step = static_cast<long>(nchan) * ninput;
-  uint32_t raw[N];
-#pragma unroll
-  for (int n = 0; n < N; ++n) raw[n] = __ldg(p + n * step);
-#pragma unroll
-  for (int n = 0; n < N; ++n) unpack4(raw[n], re[n], im[n]);
-  fft_dif<N>(re, im);
+  uint32_t raw[(N + 3) / 4];
+  load_raw<N>(in, frame, chan, input, nchan, ninput, raw);
+  fft_raw<N>(raw, re, im);
 }
 
 constexpr int UPCHAN_WARPS = 4;
@@ -174,16 +191,19 @@ __global__ void __launch_bounds__(BF_FR * 32) upchan_beamform_kernel(const uint8
     for (int b = 0; b < BF_BC; ++b)
 #pragma unroll
       for (int q = 0; q < BF_FR; ++q) acc[b][q] = make_float2(0.f, 0.f);
+    uint32_t raw[(N + 3) / 4];   // the next block's samples, fetched while phase 2 of the current one runs
+    if (valid && lane < ninput) load_raw<N>(in, frame0 + warp, chan, lane, nchan, ninput, raw);
     for (int blk = 0; blk < nblk; ++blk) {
       const int i0 = blk * 32;
       const int nv = min(32, ninput - i0);
       __syncthreads();   // phase 2 of the previous block has finished with the tiles
       if (valid && lane < nv) {
         float re[N], im[N];
-        load_fft<N>(in, frame0 + warp, chan, i0 + lane, nchan, ninput, re, im);
+        fft_raw<N>(raw, re, im);
 #pragma unroll
         for (int j = 0; j < N; ++j) tile[warp * TILE_F2 + tile_idx(lane * N + bitrev(j, N))] = make_float2(re[j], im[j]);
       }
+      if (valid && i0 + 32 + lane < ninput) load_raw<N>(in, frame0 + warp, chan, i0 + 32 + lane, nchan, ninput, raw);
       __syncthreads();
       const float2* wrow = w + (static_cast<long>(b0) * nchan + chan) * ninput * N + static_cast<long>(i0) * N;
       for (int j = warp; j < N; j += BF_FR) {
