@@ -84,25 +84,21 @@ __device__ __forceinline__ void unpack4(uint32_t b, float& r, float& i) {
   i = static_cast<float>(static_cast<int>(static_cast<int8_t>(b << 4)) >> 4);
 }
 
-// Raw bytes of series (frame, chan, input), sample n in byte n % 4 of word n / 4.  in: u8 [nframe][N][nchan][ninput].
+// Raw samples of series (frame, chan, input), one per register (left unpacked so that nothing waits on the loads
+// until the transform reads them).  in: u8 [nframe][N][nchan][ninput].
 template <int N>
 __device__ __forceinline__ void load_raw(const uint8_t* __restrict__ in, long frame, int chan, int input, int nchan,
-                                         int ninput, uint32_t (&raw)[(N + 3) / 4]) {
+                                         int ninput, uint32_t (&raw)[N]) {
   const uint8_t* p = in + ((frame * N) * nchan + chan) * static_cast<long>(ninput) + input;
   const long step = static_cast<long>(nchan) * ninput;
-  uint32_t b[N];
 #pragma unroll
-  for (int n = 0; n < N; ++n) b[n] = __ldg(p + n * step);
-#pragma unroll
-  for (int q = 0; q < (N + 3) / 4; ++q) raw[q] = 0;
-#pragma unroll
-  for (int n = 0; n < N; ++n) raw[n >> 2] |= b[n] << (8 * (n & 3));
+  for (int n = 0; n < N; ++n) raw[n] = __ldg(p + n * step);
 }
 
 template <int N>
-__device__ __forceinline__ void fft_raw(const uint32_t (&raw)[(N + 3) / 4], float (&re)[N], float (&im)[N]) {
+__device__ __forceinline__ void fft_raw(const uint32_t (&raw)[N], float (&re)[N], float (&im)[N]) {
 #pragma unroll
-  for (int n = 0; n < N; ++n) unpack4(raw[n >> 2] >> (8 * (n & 3)), re[n], im[n]);
+  for (int n = 0; n < N; ++n) unpack4(raw[n], re[n], im[n]);
   fft_dif<N>(re, im);
 }
 
@@ -110,7 +106,7 @@ __device__ __forceinline__ void fft_raw(const uint32_t (&raw)[(N + 3) / 4], floa
 template <int N>
 __device__ __forceinline__ void load_fft(const uint8_t* __restrict__ in, long frame, int chan, int input, int nchan,
                                          int ninput, float (&re)[N], float (&im)[N]) {
-  uint32_t raw[(N + 3) / 4];
+  uint32_t raw[N];
   load_raw<N>(in, frame, chan, input, nchan, ninput, raw);
   fft_raw<N>(raw, re, im);
 }
@@ -161,6 +157,10 @@ __global__ void __launch_bounds__(UPCHAN_WARPS * 32) upchan_fft_kernel(const uin
 
 constexpr int BF_BC = 4;   // beams per pass over the inputs
 constexpr int BF_FR = 5;   // frames per CTA = warps per CTA (a 480-sample gulp is 15 frames of 32)
+#ifndef XENG_UPCHAN_MINB
+#define XENG_UPCHAN_MINB 4
+#endif
+constexpr int BF_MINB = XENG_UPCHAN_MINB;   // resident CTAs per SM the register budget is set for
 
 // grid (nchan, ceil(nframe / BF_FR)), BF_FR warps.  The CTA walks blocks of 32 inputs.  Phase 1: warp q transforms
 // frame frame0 + q of the block (lane = input) into its shared-memory tile.  Phase 2: the warps split the block's
@@ -170,7 +170,7 @@ constexpr int BF_FR = 5;   // frames per CTA = warps per CTA (a 480-sample gulp 
 // k = lane % N and keeps BF_BC x BF_FR running sums; warps and the 32 / N input groups are folded at the end.
 // w: cf32 [nbeam][nchan][ninput][N];  out: cf32 [nframe][nbeam][nchan][N].
 template <int N>
-__global__ void __launch_bounds__(BF_FR * 32) upchan_beamform_kernel(const uint8_t* __restrict__ in,
+__global__ void __launch_bounds__(BF_FR * 32, BF_MINB) upchan_beamform_kernel(const uint8_t* __restrict__ in,
                                                                      const float2* __restrict__ w,
                                                                      float2* __restrict__ out, int nframe, int nchan,
                                                                      int ninput, int nbeam) {
@@ -182,6 +182,10 @@ __global__ void __launch_bounds__(BF_FR * 32) upchan_beamform_kernel(const uint8
   const long frame0 = static_cast<long>(blockIdx.y) * BF_FR;
   const bool valid = frame0 + warp < nframe;
   const int nblk = (ninput + 31) >> 5;
+  // gridDim.z = 2 splits the inputs between two CTAs that add their sums into the (zeroed) output: two addends
+  // commute, so the result does not depend on which CTA arrives first
+  const int blk_lo = static_cast<int>(static_cast<long>(nblk) * blockIdx.z / gridDim.z);
+  const int blk_hi = static_cast<int>(static_cast<long>(nblk) * (blockIdx.z + 1) / gridDim.z);
   const long wbeam = static_cast<long>(nchan) * ninput * N;
   for (int b0 = 0; b0 < nbeam; b0 += BF_BC) {
     if (!valid)   // a frame past the end contributes zeros (its outputs are not written)
@@ -191,35 +195,45 @@ __global__ void __launch_bounds__(BF_FR * 32) upchan_beamform_kernel(const uint8
     for (int b = 0; b < BF_BC; ++b)
 #pragma unroll
       for (int q = 0; q < BF_FR; ++q) acc[b][q] = make_float2(0.f, 0.f);
-    uint32_t raw[(N + 3) / 4];   // the next block's samples, fetched while phase 2 of the current one runs
-    if (valid && lane < ninput) load_raw<N>(in, frame0 + warp, chan, lane, nchan, ninput, raw);
-    for (int blk = 0; blk < nblk; ++blk) {
+    // weights of this lane's element j of block blk for the BF_BC beams of this pass (zeros outside the data)
+    auto load_w = [&](int blk, int j, float2 (&c)[BF_BC]) {
+      const int f = j * 32 + lane;
+      const bool ok = f < min(32, ninput - blk * 32) * N;
+      const float2* p = w + (static_cast<long>(b0) * nchan + chan) * ninput * N + static_cast<long>(blk) * 32 * N + f;
+#pragma unroll
+      for (int b = 0; b < BF_BC; ++b) c[b] = (ok && b0 + b < nbeam) ? __ldg(p + b * wbeam) : make_float2(0.f, 0.f);
+    };
+    // the weight loads run one element ahead of the arithmetic, across block boundaries, so their latency hides
+    // behind the previous element's work (or the next block's transform)
+    float2 cn[BF_BC];
+    if (warp < N && blk_lo < blk_hi) load_w(blk_lo, warp, cn);
+    for (int blk = blk_lo; blk < blk_hi; ++blk) {
       const int i0 = blk * 32;
       const int nv = min(32, ninput - i0);
       __syncthreads();   // phase 2 of the previous block has finished with the tiles
       if (valid && lane < nv) {
         float re[N], im[N];
-        fft_raw<N>(raw, re, im);
+        load_fft<N>(in, frame0 + warp, chan, i0 + lane, nchan, ninput, re, im);
 #pragma unroll
         for (int j = 0; j < N; ++j) tile[warp * TILE_F2 + tile_idx(lane * N + bitrev(j, N))] = make_float2(re[j], im[j]);
       }
-      if (valid && i0 + 32 + lane < ninput) load_raw<N>(in, frame0 + warp, chan, i0 + 32 + lane, nchan, ninput, raw);
       __syncthreads();
-      const float2* wrow = w + (static_cast<long>(b0) * nchan + chan) * ninput * N + static_cast<long>(i0) * N;
       for (int j = warp; j < N; j += BF_FR) {
+        float2 c[BF_BC];
+#pragma unroll
+        for (int b = 0; b < BF_BC; ++b) c[b] = cn[b];
+        if (j + BF_FR < N) load_w(blk, j + BF_FR, cn);
+        else if (blk + 1 < blk_hi) load_w(blk + 1, warp, cn);
         const int f = j * 32 + lane;   // = input_in_block * N + k
         if (f < nv * N) {
-          float2 c[BF_BC];
-#pragma unroll
-          for (int b = 0; b < BF_BC; ++b) c[b] = (b0 + b < nbeam) ? __ldg(wrow + b * wbeam + f) : make_float2(0.f, 0.f);
           const int ti = tile_idx(f);
 #pragma unroll
           for (int q = 0; q < BF_FR; ++q) {
             const float2 x = tile[q * TILE_F2 + ti];
 #pragma unroll
             for (int b = 0; b < BF_BC; ++b) {
-              acc[b][q].x += c[b].x * x.x - c[b].y * x.y;
-              acc[b][q].y += c[b].x * x.y + c[b].y * x.x;
+              acc[b][q].x = fmaf(c[b].x, x.x, fmaf(-c[b].y, x.y, acc[b][q].x));
+              acc[b][q].y = fmaf(c[b].x, x.y, fmaf(c[b].y, x.x, acc[b][q].y));
             }
           }
         }
@@ -250,7 +264,13 @@ __global__ void __launch_bounds__(BF_FR * 32) upchan_beamform_kernel(const uint8
           s.x += r.x;
           s.y += r.y;
         }
-        out[(((frame0 + q) * nbeam + b0 + b) * nchan + chan) * N + k] = s;
+        float2* o = out + (((frame0 + q) * nbeam + b0 + b) * nchan + chan) * N + k;
+        if (gridDim.z == 1) {
+          *o = s;
+        } else {
+          atomicAdd(&o->x, s.x);
+          atomicAdd(&o->y, s.y);
+        }
       }
     }
     __syncthreads();
@@ -266,7 +286,12 @@ cudaError_t fft_n(const uint8_t* in, float2* out, long nframe, int nchan, int ni
 template <int N>
 cudaError_t bf_n(const uint8_t* in, const float2* w, float2* out, long nframe, int nchan, int ninput, int nbeam,
                  cudaStream_t st) {
-  dim3 grid(nchan, static_cast<unsigned>((nframe + BF_FR - 1) / BF_FR));
+  const int split = ninput >= 128 ? 2 : 1;
+  if (split > 1) {
+    cudaError_t e = cudaMemsetAsync(out, 0, sizeof(float2) * nframe * nbeam * nchan * N, st);
+    if (e != cudaSuccess) return e;
+  }
+  dim3 grid(nchan, static_cast<unsigned>((nframe + BF_FR - 1) / BF_FR), split);
   upchan_beamform_kernel<N><<<grid, BF_FR * 32, 0, st>>>(in, w, out, static_cast<int>(nframe), nchan, ninput, nbeam);
   return cudaGetLastError();
 }

@@ -107,6 +107,12 @@ def test_upchan_beamform_equals_fft_then_weighted_sum_on_device(torch_cuda):
     want = torch.einsum("bcik,fcik->fbck", wc, Xc)
     got = torch.view_as_complex(out).to(torch.complex128)
     assert ((got - want).abs().max() / want.abs().max()).item() <= TOL
+    # the two input halves are summed into the output with atomics; two addends commute, so reruns are bit-equal
+    for _ in range(3):
+        again = torch.full_like(out, float("nan"))
+        ops.upchan_beamform(v, w, again, nframe, nfine, nchan, ninput, nbeam)
+        torch.cuda.synchronize()
+        assert torch.equal(again, out)
 
 
 def test_upchan_argument_errors(torch_cuda):
