@@ -13,7 +13,10 @@ so the oracle follows the reference's own numpy restatements and is pinned
 against fixtures produced by *executing those reference functions*
 (``tests/golden/make_golden.py`` imports them from /root/reference with the
 absent ``bifrost``/``ujson``/``etcd3`` modules stubbed) -- see
-``tests/test_oracle_golden.py``.
+``tests/test_oracle_golden.py``.  Exception: the offline upchannelise functions at
+the end restate stock bifrost blocks for which the reference holds
+no test or vector -- for those, PARITY UNPINNED by reference vectors; they are
+checked against the literal DFT definition only.
 
 Every function cites the reference file:line it follows (paths relative to
 /root/reference).
