@@ -117,11 +117,14 @@ __global__ void __launch_bounds__(1024) reorder_kernel(const int32_t* __restrict
 enum { RO_FULL = 0, RO_COR = 1, RO_PY = 2 };
 constexpr int RO_ROW = 4 * 32 + 1;   // int2 per k row: 4 pol products x 32 channels, +1 keeps STS.64 conflict-free
 
+constexpr int RO_TY = 8;              // warps per block; each walks 32 / RO_TY rows of the 32 x 32 tile
+constexpr int RO_R = 32 / RO_TY;
+
 template <int MODE>
-__global__ void __launch_bounds__(1024) reorder_tile_kernel(const int32_t* __restrict__ in, int2* __restrict__ out,
-                                                            const int32_t* __restrict__ a2bl,
-                                                            const int32_t* __restrict__ conj, int nstand, int nchan,
-                                                            long W, long plane_words, int nchunk) {
+__global__ void __launch_bounds__(32 * RO_TY) reorder_tile_kernel(const int32_t* __restrict__ in, int2* __restrict__ out,
+                                                                  const int32_t* __restrict__ a2bl,
+                                                                  const int32_t* __restrict__ conj, int nstand, int nchan,
+                                                                  long W, long plane_words, int nchunk) {
   __shared__ int2 tile[32 * RO_ROW];
   __shared__ int tab[32 * 4];                              // word index | conj << 31 of the block's 32 x 4 entries
   // blockIdx.x walks the (parity, chunk) groups; group g = 2 jc + par holds the second stands s1 >= its first s0
@@ -146,45 +149,60 @@ __global__ void __launch_bounds__(1024) reorder_tile_kernel(const int32_t* __res
       }
     }
     __syncthreads();
-    {  // gather: lanes along the 32 first stands, warps along channel
+    {  // gather: lanes along the 32 first stands, warps along channel; all 8 * RO_R loads of a thread are in flight
+       // before the first one is used
       const int s0 = s0_first + 2 * threadIdx.x;
-      const int c = c0 + threadIdx.y;
-      if (s0 <= s1 && c < nchan) {
-        const int32_t* pre = in + static_cast<long>(c) * W;
-        const int32_t* pim = pre + plane_words;
+      if (s0 <= s1) {
         const int4 t4 = *reinterpret_cast<const int4*>(tab + threadIdx.x * 4);
         const int tt[4] = {t4.x, t4.y, t4.z, t4.w};
-        int re[4], im[4];
+        int re[RO_R][4], im[RO_R][4];
 #pragma unroll
-        for (int pp = 0; pp < 4; ++pp) {
-          re[pp] = __ldg(pre + (tt[pp] & 0x7fffffff));
-          im[pp] = __ldg(pim + (tt[pp] & 0x7fffffff));
+        for (int r = 0; r < RO_R; ++r) {
+          const int c = c0 + threadIdx.y + RO_TY * r;
+          if (c < nchan) {
+            const int32_t* pre = in + static_cast<long>(c) * W;
+            const int32_t* pim = pre + plane_words;
+#pragma unroll
+            for (int pp = 0; pp < 4; ++pp) {
+              re[r][pp] = __ldg(pre + (tt[pp] & 0x7fffffff));
+              im[r][pp] = __ldg(pim + (tt[pp] & 0x7fffffff));
+            }
+          }
         }
 #pragma unroll
-        for (int pp = 0; pp < 4; ++pp)
-          tile[threadIdx.x * RO_ROW + pp * 32 + threadIdx.y] = make_int2(re[pp], tt[pp] < 0 ? -im[pp] : im[pp]);
+        for (int r = 0; r < RO_R; ++r) {
+          const int cy = threadIdx.y + RO_TY * r;
+          if (c0 + cy < nchan) {
+#pragma unroll
+            for (int pp = 0; pp < 4; ++pp)
+              tile[threadIdx.x * RO_ROW + pp * 32 + cy] = make_int2(re[r][pp], tt[pp] < 0 ? -im[r][pp] : im[r][pp]);
+          }
+        }
       }
     }
     __syncthreads();
-    {  // scatter: lanes along channel, warps along the 32 first stands
-      const int s0 = s0_first + 2 * threadIdx.y;
-      const int c = c0 + threadIdx.x;
+    // scatter: lanes along channel, warps along the 32 first stands
+    const int c = c0 + threadIdx.x;
+#pragma unroll
+    for (int r = 0; r < RO_R; ++r) {
+      const int ky = threadIdx.y + RO_TY * r;
+      const int s0 = s0_first + 2 * ky;
       if (s0 <= s1 && c < nchan && !(mirror && s0 == s1)) {
-        const int2* t = tile + threadIdx.y * RO_ROW + threadIdx.x;
+        const int2* t = tile + ky * RO_ROW + threadIdx.x;
         if (MODE == RO_FULL) {
           const long e = ((mirror ? static_cast<long>(s1) * nstand + s0 : static_cast<long>(s0) * nstand + s1)) * 4;
 #pragma unroll
-          for (int pp = 0; pp < 4; ++pp) out[(e + pp) * nchan + c] = t[pp * 32];
+          for (int pp = 0; pp < 4; ++pp) __stcs(out + (e + pp) * nchan + c, t[pp * 32]);
         } else {
           const long bl = static_cast<long>(s0) * nstand - (static_cast<long>(s0) * (s0 - 1)) / 2 + (s1 - s0);
           if (MODE == RO_PY) {
 #pragma unroll
-            for (int pp = 0; pp < 4; ++pp) out[(bl * 4 + pp) * nchan + c] = t[pp * 32];
+            for (int pp = 0; pp < 4; ++pp) __stcs(out + (bl * 4 + pp) * nchan + c, t[pp * 32]);
           } else {
             int4* o = reinterpret_cast<int4*>(out + (bl * nchan + c) * 4);
             const int2 v0 = t[0], v1 = t[32], v2 = t[64], v3 = t[96];
-            o[0] = make_int4(v0.x, v0.y, v1.x, v1.y);
-            o[1] = make_int4(v2.x, v2.y, v3.x, v3.y);
+            __stcs(o, make_int4(v0.x, v0.y, v1.x, v1.y));
+            __stcs(o + 1, make_int4(v2.x, v2.y, v3.x, v3.y));
           }
         }
       }
@@ -251,9 +269,9 @@ cudaError_t launch_reorder(const int32_t* in, int32_t* out, const int32_t* a2bl,
   int2* o = reinterpret_cast<int2*>(out);
   const long plane = static_cast<long>(nchan) * W;
   switch (layout) {
-    case RO_FULL: reorder_tile_kernel<RO_FULL><<<grid, dim3(32, 32), 0, stream>>>(in, o, a2bl, conj, nstand, nchan, W, plane, nchunk); break;
-    case RO_COR: reorder_tile_kernel<RO_COR><<<grid, dim3(32, 32), 0, stream>>>(in, o, a2bl, conj, nstand, nchan, W, plane, nchunk); break;
-    case RO_PY: reorder_tile_kernel<RO_PY><<<grid, dim3(32, 32), 0, stream>>>(in, o, a2bl, conj, nstand, nchan, W, plane, nchunk); break;
+    case RO_FULL: reorder_tile_kernel<RO_FULL><<<grid, dim3(32, RO_TY), 0, stream>>>(in, o, a2bl, conj, nstand, nchan, W, plane, nchunk); break;
+    case RO_COR: reorder_tile_kernel<RO_COR><<<grid, dim3(32, RO_TY), 0, stream>>>(in, o, a2bl, conj, nstand, nchan, W, plane, nchunk); break;
+    case RO_PY: reorder_tile_kernel<RO_PY><<<grid, dim3(32, RO_TY), 0, stream>>>(in, o, a2bl, conj, nstand, nchan, W, plane, nchunk); break;
     default: return cudaErrorInvalidValue;
   }
   return cudaGetLastError();
