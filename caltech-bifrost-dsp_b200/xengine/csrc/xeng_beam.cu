@@ -201,7 +201,9 @@ constexpr int PW_T = 1024;
 __global__ void __launch_bounds__(256) beam_integrate_kernel(const float2* __restrict__ in, float4* __restrict__ out,
                                                              int nchan, int nbeam, int ntime, int ntime_sum,
                                                              int beam0, int nbeam_out) {
-  __shared__ float4 prod[PW_T];
+  // products of output block T start at element T * (ntime_sum + 1): the one-element skew keeps the lanes of the
+  // summing pass (one per output block, stride ntime_sum float4) off each other's banks for even ntime_sum
+  __shared__ float4 prod[2 * PW_T];
   const int c = blockIdx.x, p = blockIdx.y;
   const float2* X = in + (static_cast<long>(c) * nbeam + 2 * (beam0 + p)) * ntime;
   const float2* Y = X + ntime;
@@ -226,17 +228,19 @@ __global__ void __launch_bounds__(256) beam_integrate_kernel(const float2* __res
     const int n = min(span, nblk * ntime_sum - tbase);
     for (int k = threadIdx.x; k < n; k += blockDim.x) {
       const float2 x = X[tbase + k], y = Y[tbase + k];
-      prod[k] = make_float4(x.x * x.x + x.y * x.y, y.x * y.x + y.y * y.y, x.x * y.x + x.y * y.y,
-                            x.y * y.x - x.x * y.y);
+      prod[k + k / ntime_sum] = make_float4(x.x * x.x + x.y * x.y, y.x * y.x + y.y * y.y, x.x * y.x + x.y * y.y,
+                                            x.y * y.x - x.x * y.y);
     }
     __syncthreads();
-    for (int T = threadIdx.x; T < n / ntime_sum; T += blockDim.x) {
-      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int k = 0; k < ntime_sum; ++k) {
-        const float4 q = prod[T * ntime_sum + k];
-        s.x += q.x; s.y += q.y; s.z += q.z; s.w += q.w;
-      }
-      out[(static_cast<long>(p) * nblk + tbase / ntime_sum + T) * nchan + c] = s;
+    // one thread per (output block, Stokes-like component): 4x the threads of a float4-per-thread pass, each
+    // component still summed in time order
+    const float* prodf = reinterpret_cast<const float*>(prod);
+    float* outf = reinterpret_cast<float*>(out);
+    for (int e = threadIdx.x; e < 4 * (n / ntime_sum); e += blockDim.x) {
+      const int T = e >> 2, comp = e & 3;
+      float s = 0.f;
+      for (int k = 0; k < ntime_sum; ++k) s += prodf[(T * (ntime_sum + 1) + k) * 4 + comp];
+      outf[((static_cast<long>(p) * nblk + tbase / ntime_sum + T) * nchan + c) * 4 + comp] = s;
     }
     __syncthreads();
   }

@@ -127,6 +127,7 @@ __global__ void __launch_bounds__(32 * RO_TY) reorder_tile_kernel(const int32_t*
                                                                   long W, long plane_words, int nchunk) {
   __shared__ int2 tile[32 * RO_ROW];
   __shared__ int tab[32 * 4];                              // word index | conj << 31 of the block's 32 x 4 entries
+  __shared__ int tab2[32 * 4];                             // RO_FULL: tile slot | flip << 31 of the mirrored entries
   // blockIdx.x walks the (parity, chunk) groups; group g = 2 jc + par holds the second stands s1 >= its first s0
   int s0_first = 0, s1 = blockIdx.x;
   for (int g = 0; g < 2 * nchunk; ++g) {
@@ -139,6 +140,47 @@ __global__ void __launch_bounds__(32 * RO_TY) reorder_tile_kernel(const int32_t*
   const int c0 = blockIdx.y * 32;
 #pragma unroll 1
   for (int mirror = 0; mirror < (MODE == RO_FULL ? 2 : 1); ++mirror) {
+    if (MODE == RO_FULL && mirror) {
+      // The mirrored entry [s1][s0][p][q] normally names a word the first pass already gathered (the same product,
+      // conjugated).  Look it up among the 4 words of this stand pair instead of gathering again; a map for which
+      // that fails anywhere in the block takes the general path below.
+      int ok = 1;
+      if (threadIdx.y < 4) {
+        const int s0 = s0_first + 2 * threadIdx.x;
+        if (s0 <= s1) {
+          const long e = (static_cast<long>(s1) * nstand + s0) * 4 + threadIdx.y;
+          const int wm = __ldg(a2bl + e), cm = __ldg(conj + e) ? 1 : 0;
+          int found = -1;
+#pragma unroll
+          for (int pp = 0; pp < 4; ++pp) {
+            const int t1 = tab[threadIdx.x * 4 + pp];
+            if ((t1 & 0x7fffffff) == wm) found = pp | ((cm != ((t1 >> 31) & 1)) ? 0x80000000 : 0);
+          }
+          ok = found != -1;
+          tab2[threadIdx.x * 4 + threadIdx.y] = found;
+        }
+      }
+      if (__syncthreads_and(ok)) {
+        const int c = c0 + threadIdx.x;
+#pragma unroll
+        for (int r = 0; r < RO_R; ++r) {
+          const int ky = threadIdx.y + RO_TY * r;
+          const int s0 = s0_first + 2 * ky;
+          if (s0 < s1 && c < nchan) {
+            const int2* t = tile + ky * RO_ROW + threadIdx.x;
+            const long e = (static_cast<long>(s1) * nstand + s0) * 4;
+#pragma unroll
+            for (int pp = 0; pp < 4; ++pp) {
+              const int m = tab2[ky * 4 + pp];
+              int2 v = t[(m & 3) * 32];
+              if (m < 0) v.y = -v.y;
+              __stcs(out + (e + pp) * nchan + c, v);
+            }
+          }
+        }
+        break;
+      }
+    }
     if (mirror) __syncthreads();
     if (threadIdx.y < 4) {  // table entries once per block, not once per channel
       const int s0 = s0_first + 2 * threadIdx.x;

@@ -25,3 +25,7 @@ timeout 300 python scripts/prof_upchan.py > gpurun_out/${TAG}_upchan_plain.log 2
 timeout 600 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,lts__t_bytes.sum,sm__warps_active.avg.pct_of_peak_sustained_active --clock-control none \
     -k regex:"upchan_" -c 12 --csv \
     --log-file gpurun_out/${TAG}_upchan_kernels.csv python scripts/prof_upchan.py > gpurun_out/${TAG}_ncu5.log 2>&1; echo "ncu upchan rc=$?"
+timeout 300 ncu --set full --clock-control none --import-source on -k regex:upchan_beamform -s 1 -c 1 \
+    -f -o gpurun_out/${TAG}_upchan_bf python scripts/prof_upchan.py > gpurun_out/${TAG}_ncu6.log 2>&1; echo "ncu upchan full rc=$?"
+# the reference arm (CPU formulation on the host cores), as the driver runs it
+timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${TAG}_bench_reference.json 2> gpurun_out/${TAG}_bench_reference.err; echo "reference arm rc=$?"

@@ -360,3 +360,21 @@ def test_corr_baseline_size_properties(torch_cuda):
     for c in (0, 191, 383):
         assert np.array_equal(got[:, c:c + 1], orc.corr_xgpu(vh[:, c:c + 1]))
     xc.close()
+
+
+def test_reorder_arbitrary_tables_take_the_general_path(torch_cuda):
+    """xeng_reorder is table-driven: with a2bl / conj tables that are NOT what get_order builds (random word indices,
+    so a mirrored entry is not one of the four words of its stand pair) the kernel must fall back from the
+    tile-reuse shortcut to gathering every entry, and still equal the oracle's plain gather."""
+    from xengine import ops
+    torch = torch_cuda
+    nstand, nchan = 40, 37
+    rng = np.random.default_rng(99)
+    wpc = ops.words_per_chan(nstand)
+    x = rng.integers(-2**31, 2**31 - 1, size=(2, nchan, wpc), dtype=np.int64).astype(np.int32)
+    a2bl = rng.integers(0, wpc, size=(nstand, nstand, 2, 2)).astype(np.int32)
+    conj = rng.integers(0, 2, size=(nstand, nstand, 2, 2)).astype(np.int32)
+    full = torch.full((nstand, nstand, 2, 2, nchan, 2), 0x5a5a5a5a, dtype=torch.int32, device="cuda")
+    ops.reorder(torch.from_numpy(x).cuda(), full, torch.from_numpy(a2bl).cuda(), torch.from_numpy(conj).cuda(),
+                nstand, 2, nchan, wpc)
+    assert np.array_equal(full.cpu().numpy(), orc.reorder(x, a2bl, conj))
