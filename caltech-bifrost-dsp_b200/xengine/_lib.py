@@ -50,6 +50,8 @@ SIGNATURES = {
     "xeng_bf_destroy": (_i, [_vp]),
     "xeng_bf_set_stream": (_i, [_vp, _vp]),
     "xeng_bf_run": (_i, [_vp, _vp, _vp, _vp]),
+    "xeng_bf_set_weights": (_i, [_vp, _vp]),
+    "xeng_bf_set_impl": (_i, [_vp, _i]),
     "xeng_bf_integrate": (_i, [_vp, _vp, _vp, _i]),
     "xeng_bf_integrate_single": (_i, [_vp, _vp, _vp, _i, _i]),
     "xeng_bf_run_integrate": (_i, [_vp, _vp, _vp, _vp, _i]),

@@ -61,13 +61,24 @@ struct xeng_corr_s {
   int32_t* d_sub_vismap;     // [nvis] device copies for the unfused fallback
   int32_t* d_sub_conj;
   int32_t* d_sub_scratch;    // per-gulp visibilities, unfused fallback only
+  // developer-only profiling switches, read ONCE at create time and announced on stderr (results are invalid
+  // while ablate != 0); never consulted per launch
+  int ablate;
+  char trace_path[256];
+  long long* d_trace;
 };
 
 struct xeng_bf_s {
-  int device, ninput, nchan, ntime, nbeam, ntime_blocks;
+  int device, ninput, nchan, ntime, nbeam, ntime_blocks, nsm;
   cudaStream_t stream;
   float2* d_volt;   // scratch voltage beams for xeng_bf_run_integrate when the voltage tap is on
   int tap;          // xeng_bf_set_tap: keep the voltage beams (two kernels) instead of the fused power epilogue
+  int impl;         // 0: tensor cores when the shape allows (default), 1: fp32 FMA kernel (cross-check)
+  // tensor-core path: the weights as int8 digit planes + per-(channel, beam) scales (xeng_beam_tc.cu)
+  int8_t* d_wdig;
+  float* d_wscale;
+  bool w_loaded;            // d_wdig / d_wscale hold the weights last given to set_weights / run
+  const float2* w_f32;      // the caller's fp32 weights last given to set_weights (fp32 path with d_w == NULL)
 };
 
 extern "C" {
@@ -111,6 +122,12 @@ int xeng_corr_create(xeng_corr_t* out, int nstand, int npol, int nchan, int ntim
     delete h;
     return fail(XENG_ERR_CUDA, "xeng_corr_create: %s", cudaGetErrorString(e));
   }
+  if (const char* ab = getenv("XENG_CORR_ABLATE")) h->ablate = atoi(ab);
+  if (const char* tp = getenv("XENG_CORR_TRACE")) snprintf(h->trace_path, sizeof(h->trace_path), "%s", tp);
+  if (h->ablate || h->trace_path[0])
+    fprintf(stderr, "libxeng: DEVELOPER PROFILING MODE on this Corr handle (XENG_CORR_ABLATE=%d, XENG_CORR_TRACE=%s): "
+                    "visibilities are INVALID while the ablation mask is non-zero\n", h->ablate,
+            h->trace_path[0] ? h->trace_path : "");
   *out = h;
   return XENG_OK;
 }
@@ -126,6 +143,7 @@ int xeng_corr_destroy(xeng_corr_t h) {
   if (h->d_sub_vismap) cudaFree(h->d_sub_vismap);
   if (h->d_sub_conj) cudaFree(h->d_sub_conj);
   if (h->d_sub_scratch) cudaFree(h->d_sub_scratch);
+  if (h->d_trace) cudaFree(h->d_trace);
   if (h->h_err) cudaFreeHost(h->h_err);
   delete h;
   return XENG_OK;
@@ -156,20 +174,16 @@ static int corr_launch(xeng_corr_t h, const void* d_in, int32_t* d_out, int accu
   a.tiles_per_chan = T * (T + 1) / 2;
   a.ntiles = a.tiles_per_chan * h->nchan;
   a.accumulate = accumulate;
-  {
-    const char* ab = getenv("XENG_CORR_ABLATE");   // developer-only timing ablations
-    a.ablate = ab ? atoi(ab) : 0;
-  }
+  a.ablate = h->ablate;
   a.trace = nullptr;
   a.sub_begin = h->d_sub_begin; a.sub_entries = h->d_sub_entries; a.sub_out = d_sub_out;
   a.sub_nvis = h->sub_nvis; a.sub_nsum = h->sub_nsum;
-  const char* trace_path = getenv("XENG_CORR_TRACE");   // developer-only: per-role clock64 timeline of CTA 0
-  static long long* d_trace = nullptr;
+  const char* trace_path = h->trace_path[0] ? h->trace_path : nullptr;   // developer-only: per-role timeline of CTA 0
   const size_t trace_bytes = 5 * 4096 * 2 * sizeof(long long);
   if (trace_path && a.ablate) {
-    if (!d_trace) XENG_CUDA(cudaMalloc(reinterpret_cast<void**>(&d_trace), trace_bytes));
-    XENG_CUDA(cudaMemsetAsync(d_trace, 0, trace_bytes, h->stream));
-    a.trace = d_trace;
+    if (!h->d_trace) XENG_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->d_trace), trace_bytes));
+    XENG_CUDA(cudaMemsetAsync(h->d_trace, 0, trace_bytes, h->stream));
+    a.trace = h->d_trace;
   }
   a.words_per_chan = h->words_per_chan;
   a.quad_cells = h->quad_cells;
@@ -181,7 +195,7 @@ static int corr_launch(xeng_corr_t h, const void* d_in, int32_t* d_out, int accu
     XENG_CUDA(cudaStreamSynchronize(h->stream));
     long long* host = static_cast<long long*>(malloc(trace_bytes));
     if (host) {
-      XENG_CUDA(cudaMemcpy(host, d_trace, trace_bytes, cudaMemcpyDeviceToHost));
+      XENG_CUDA(cudaMemcpy(host, h->d_trace, trace_bytes, cudaMemcpyDeviceToHost));
       FILE* f = fopen(trace_path, "wb");
       if (f) { fwrite(host, 1, trace_bytes, f); fclose(f); }
       free(host);
@@ -489,20 +503,76 @@ int xeng_bf_create(xeng_bf_t* out, int gpu, int ninput, int nchan, int ntime, in
   h->stream = nullptr;
   h->d_volt = nullptr;
   h->tap = 0;
+  h->impl = 0;
+  h->d_wdig = nullptr; h->d_wscale = nullptr; h->w_loaded = false; h->w_f32 = nullptr;
   cudaError_t e = cudaGetDevice(&h->device);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->nsm, cudaDevAttrMultiProcessorCount, h->device);
   if (e != cudaSuccess) {
     delete h;
-    return fail(XENG_ERR_CUDA, "cudaGetDevice: %s", cudaGetErrorString(e));
+    return fail(XENG_ERR_CUDA, "xeng_bf_create: %s", cudaGetErrorString(e));
   }
   *out = h;
   return XENG_OK;
 }
 int xeng_bf_destroy(xeng_bf_t h) {
-  if (h && h->d_volt) {
+  if (h) {
     cudaSetDevice(h->device);
-    cudaFree(h->d_volt);
+    if (h->d_volt) cudaFree(h->d_volt);
+    if (h->d_wdig) cudaFree(h->d_wdig);
+    if (h->d_wscale) cudaFree(h->d_wscale);
   }
   delete h;
+  return XENG_OK;
+}
+int xeng_bf_set_impl(xeng_bf_t h, int impl) {
+  if (!h) return fail(XENG_ERR_ARG, "null handle");
+  if (impl < 0 || impl > 1) return fail(XENG_ERR_ARG, "impl must be 0 (tcgen05 int8 digit planes when the shape allows) or 1 (fp32 FMA cross-check)");
+  h->impl = impl;
+  return XENG_OK;
+}
+
+// fp32 weights -> int8 digit planes (+ scales) in the handle; the digits are what the tensor-core kernel reads
+static int bf_convert_weights(xeng_bf_t h, const void* d_w) {
+  xeng::BeamTcGeom g;
+  if (!xeng::beam_tc_geometry(h->ninput, h->nchan, h->nbeam, &g)) return XENG_OK;   // fp32 path only for this shape
+  if (!h->d_wdig) {
+    XENG_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->d_wdig), g.dig_bytes));
+    XENG_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->d_wscale), g.scale_floats * sizeof(float)));
+  }
+  XENG_CUDA(xeng::launch_beam_weight_digits(static_cast<const float2*>(d_w), h->d_wdig, h->d_wscale, h->nchan,
+                                            h->nbeam, h->ninput, h->stream));
+  return XENG_OK;
+}
+
+int xeng_bf_set_weights(xeng_bf_t h, const void* d_w) {
+  if (!h || !d_w) return fail(XENG_ERR_ARG, "null pointer");
+  XENG_CUDA(cudaSetDevice(h->device));
+  int rc = bf_convert_weights(h, d_w);
+  if (rc) return rc;
+  h->w_loaded = true;
+  h->w_f32 = static_cast<const float2*>(d_w);
+  return XENG_OK;
+}
+
+// One beamformer launch: tensor cores when the shape allows, else (or impl == 1) the fp32 FMA kernel.
+// d_w != NULL: the reference's calling convention (weights with every call) -- converted on the stream first.
+// d_w == NULL: the weights last loaded with xeng_bf_set_weights.
+static int bf_launch(xeng_bf_t h, xeng::BeamArgs& a, const void* d_w) {
+  if (h->impl == 0 && xeng::beam_tc_supported(a)) {
+    if (d_w) {
+      int rc = bf_convert_weights(h, d_w);
+      if (rc) return rc;
+      h->w_loaded = true;
+      h->w_f32 = static_cast<const float2*>(d_w);
+    } else if (!h->w_loaded) {
+      return fail(XENG_ERR_ARG, "no weights: pass d_w or call xeng_bf_set_weights first");
+    }
+    XENG_CUDA(xeng::launch_beamform_tc(a, h->d_wdig, h->d_wscale, h->nsm, h->stream));
+    return XENG_OK;
+  }
+  a.w = d_w ? static_cast<const float2*>(d_w) : h->w_f32;
+  if (!a.w) return fail(XENG_ERR_ARG, "no weights: pass d_w or call xeng_bf_set_weights first");
+  XENG_CUDA(xeng::launch_beamform(a, h->stream));
   return XENG_OK;
 }
 int xeng_bf_set_stream(xeng_bf_t h, void* s) {
@@ -512,31 +582,29 @@ int xeng_bf_set_stream(xeng_bf_t h, void* s) {
 }
 
 int xeng_bf_run(xeng_bf_t h, const void* d_in, void* d_out, const void* d_w) {
-  if (!h || !d_in || !d_out || !d_w) return fail(XENG_ERR_ARG, "null pointer");
+  if (!h || !d_in || !d_out) return fail(XENG_ERR_ARG, "null pointer");
   XENG_CUDA(cudaSetDevice(h->device));
   xeng::BeamArgs a;
   a.in = static_cast<const uint8_t*>(d_in);
-  a.w = static_cast<const float2*>(d_w);
+  a.w = nullptr;
   a.out = static_cast<float2*>(d_out);
   a.ntime = h->ntime; a.nchan = h->nchan; a.ninput = h->ninput; a.nbeam = h->nbeam;
-  XENG_CUDA(xeng::launch_beamform(a, h->stream));
-  return XENG_OK;
+  return bf_launch(h, a, d_w);
 }
 
 int xeng_bf_run_integrate(xeng_bf_t h, const void* d_in, void* d_out, const void* d_w, int ntime_sum) {
-  if (!h || !d_in || !d_out || !d_w) return fail(XENG_ERR_ARG, "null pointer");
+  if (!h || !d_in || !d_out) return fail(XENG_ERR_ARG, "null pointer");
   if (ntime_sum <= 0 || (h->nbeam & 1) || h->ntime % ntime_sum) return fail(XENG_ERR_ARG, "need ntime_sum | ntime and an even number of beams");
   XENG_CUDA(cudaSetDevice(h->device));
   if (!h->tap && ntime_sum <= xeng::beamform_fused_max_ntime_sum()) {   // one kernel, only the powers leave the SM
     xeng::BeamArgs a;
     a.in = static_cast<const uint8_t*>(d_in);
-    a.w = static_cast<const float2*>(d_w);
+    a.w = nullptr;
     a.out = nullptr;
     a.ntime = h->ntime; a.nchan = h->nchan; a.ninput = h->ninput; a.nbeam = h->nbeam;
     a.pow_out = static_cast<float*>(d_out);
     a.ntime_sum = ntime_sum;
-    XENG_CUDA(xeng::launch_beamform(a, h->stream));
-    return XENG_OK;
+    return bf_launch(h, a, d_w);
   }
   if (!h->d_volt) XENG_CUDA(cudaMalloc(reinterpret_cast<void**>(&h->d_volt), sizeof(float2) * h->nchan * h->nbeam * static_cast<size_t>(h->ntime)));
   int rc = xeng_bf_run(h, d_in, h->d_volt, d_w);

@@ -157,8 +157,7 @@ __global__ void __launch_bounds__(BF_THREADS, 2) beamform_kernel(BeamArgs a) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const float2 x = acc[2 * jp][k], y = acc[2 * jp + 1][k];
-        prod[(2 * tb + jp) * TT + (k >> 1) * (TT / 2) + 2 * tt + (k & 1)] =
-            make_float4(x.x * x.x + x.y * x.y, y.x * y.x + y.y * y.y, x.x * y.x + x.y * y.y, x.y * y.x - x.x * y.y);
+        prod[(2 * tb + jp) * TT + (k >> 1) * (TT / 2) + 2 * tt + (k & 1)] = beam_products(x, y);
       }
     }
     __syncthreads();
@@ -214,11 +213,11 @@ __global__ void __launch_bounds__(256) beam_integrate_kernel(const float2* __res
     for (int T = threadIdx.x; T < nblk; T += blockDim.x) {
       float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
       for (int k = 0; k < ntime_sum; ++k) {
-        const float2 x = X[T * ntime_sum + k], y = Y[T * ntime_sum + k];
-        s.x += x.x * x.x + x.y * x.y;
-        s.y += y.x * y.x + y.y * y.y;
-        s.z += x.x * y.x + x.y * y.y;
-        s.w += x.y * y.x - x.x * y.y;
+        const float4 pr = beam_products(X[T * ntime_sum + k], Y[T * ntime_sum + k]);
+        s.x += pr.x;
+        s.y += pr.y;
+        s.z += pr.z;
+        s.w += pr.w;
       }
       out[(static_cast<long>(p) * nblk + T) * nchan + c] = s;
     }
@@ -227,9 +226,7 @@ __global__ void __launch_bounds__(256) beam_integrate_kernel(const float2* __res
   for (int tbase = 0; tbase < nblk * ntime_sum; tbase += span) {
     const int n = min(span, nblk * ntime_sum - tbase);
     for (int k = threadIdx.x; k < n; k += blockDim.x) {
-      const float2 x = X[tbase + k], y = Y[tbase + k];
-      prod[k + k / ntime_sum] = make_float4(x.x * x.x + x.y * x.y, y.x * y.x + y.y * y.y, x.x * y.x + x.y * y.y,
-                                            x.y * y.x - x.x * y.y);
+      prod[k + k / ntime_sum] = beam_products(X[tbase + k], Y[tbase + k]);
     }
     __syncthreads();
     // one thread per (output block, Stokes-like component): 4x the threads of a float4-per-thread pass, each
@@ -274,16 +271,15 @@ cudaError_t launch_vlbi_tap(const float2* in, float2* out, int nchan, int nbeam,
 }
 
 cudaError_t launch_beamform(const BeamArgs& a, cudaStream_t stream) {
-  static bool configured = false;
-  if (!configured) {
+  cudaError_t ce = configure_once_per_device([]() -> cudaError_t {
     cudaError_t e = cudaFuncSetAttribute(beamform_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(sizeof(BeamSmem)));
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(beamform_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                static_cast<int>(sizeof(BeamSmem)));
-    if (e != cudaSuccess) return e;
-    configured = true;
-  }
+    return e;
+  }, kCfgBeam);
+  if (ce != cudaSuccess) return ce;
   if (a.ntime <= 0 || a.nchan <= 0 || a.nbeam <= 0) return cudaSuccess;
   if (a.pow_out) {                                          // fused power integration
     if (a.ntime_sum <= 0 || a.ntime_sum > TT || (a.nbeam & 1)) return cudaErrorInvalidValue;

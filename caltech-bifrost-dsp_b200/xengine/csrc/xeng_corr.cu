@@ -308,12 +308,10 @@ __global__ void corr_simt_kernel(CorrArgs a) {
 int corr_tc_smem_bytes() { return SMEM_BYTES; }
 
 cudaError_t launch_corr_tc(const CorrArgs& a, int nsm, cudaStream_t stream) {
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(corr_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
-    if (e != cudaSuccess) return e;
-    configured = true;
-  }
+  cudaError_t ce = configure_once_per_device([]() -> cudaError_t {
+    return cudaFuncSetAttribute(corr_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+  }, kCfgCorrTc);
+  if (ce != cudaSuccess) return ce;
   int grid = a.ntiles < nsm ? a.ntiles : nsm;
   if (grid <= 0) return cudaSuccess;
   corr_tc_kernel<<<grid, N_THREADS, SMEM_BYTES, stream>>>(a);

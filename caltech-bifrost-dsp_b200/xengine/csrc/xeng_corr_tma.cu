@@ -484,16 +484,20 @@ bool corr_tma_supported(const CorrArgs& a) {
 
 cudaError_t launch_corr_swz(const CorrArgs& a_in, int nsm, cudaStream_t stream) {
   CorrArgs a = a_in;
-  static EncodeTiledFn encode = nullptr;
-  static bool configured = false;
-  if (!configured) {
+  static EncodeTiledFn encode = nullptr;     // driver entry point: process-wide, not per device
+  static std::once_flag encode_once;
+  static cudaError_t encode_err = cudaSuccess;
+  std::call_once(encode_once, []() {
     void* fn = nullptr;
     cudaDriverEntryPointQueryResult qres;
-    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
-    if (e != cudaSuccess) return e;
-    if (qres != cudaDriverEntryPointSuccess || !fn) return cudaErrorNotSupported;
-    encode = reinterpret_cast<EncodeTiledFn>(fn);
-    e = cudaFuncSetAttribute(corr_swz_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    encode_err = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (encode_err == cudaSuccess && (qres != cudaDriverEntryPointSuccess || !fn)) encode_err = cudaErrorNotSupported;
+    if (encode_err == cudaSuccess) encode = reinterpret_cast<EncodeTiledFn>(fn);
+  });
+  if (encode_err != cudaSuccess) return encode_err;
+  // function attributes and the __constant__ tile table live in the device's context: once per device
+  cudaError_t ce = configure_once_per_device([]() -> cudaError_t {
+    cudaError_t e = cudaFuncSetAttribute(corr_swz_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(corr_swz_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e == cudaSuccess)
@@ -507,9 +511,9 @@ cudaError_t launch_corr_swz(const CorrArgs& a_in, int nsm, cudaStream_t stream) 
       }
     e = cudaMemcpyToSymbol(c_tile_I, tab_i, sizeof(tab_i));
     if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_tile_J, tab_j, sizeof(tab_j));
-    if (e != cudaSuccess) return e;
-    configured = true;
-  }
+    return e;
+  }, kCfgCorrSwz);
+  if (ce != cudaSuccess) return ce;
   int grid = a.ntiles < nsm ? a.ntiles : nsm;
   if (grid <= 0) return cudaSuccess;
   a.step_c = grid / a.tiles_per_chan;

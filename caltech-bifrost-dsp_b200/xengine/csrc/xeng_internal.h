@@ -1,9 +1,30 @@
 // Internal (non-ABI) declarations shared by the kernel translation units and xeng_api.cu.
 #pragma once
 #include <cstdint>
+#include <mutex>
 #include <cuda_runtime.h>
 
 namespace xeng {
+
+// Per-device one-time configuration (cudaFuncSetAttribute, __constant__ tables): function attributes and constant
+// memory belong to the device's context, so a process that holds handles on several GPUs must configure each one.
+// `fn` runs once per (key, current device), under a lock (two block threads may make their first launch together).
+enum CfgKey { kCfgCorrSwz = 0, kCfgCorrTc, kCfgBeam, kCfgBeamTc, kCfgCount };
+constexpr int kCfgMaxDevices = 64;
+template <class F>
+inline cudaError_t configure_once_per_device(F&& fn, int key) {
+  static std::mutex mu;
+  static bool done[kCfgCount][kCfgMaxDevices] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kCfgMaxDevices) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(mu);
+  if (done[key][dev]) return cudaSuccess;
+  e = fn();
+  if (e == cudaSuccess) done[key][dev] = true;
+  return e;
+}
 
 struct CorrArgs {
   const uint8_t* in;    // [ntime][nchan][ninput] 4+4-bit complex
@@ -52,6 +73,24 @@ struct BeamArgs {
   float* pow_out = nullptr;   // non-null: fused power integration, [nbeam/2][ntime/ntime_sum][nchan][4]; `out` unused
   int ntime_sum = 0, tile_t = 0;
 };
+// tensor-core beamformer (xeng_beam_tc.cu): int8 digit planes of the weights x int8 voltages, exact int32 sums
+struct BeamTcGeom {
+  int nb, nbb, nst;              // beams per block, beam blocks, 64-input K stages
+  size_t dig_bytes, scale_floats;
+};
+bool beam_tc_geometry(int ninput, int nchan, int nbeam, BeamTcGeom* g);
+bool beam_tc_supported(const BeamArgs& a);
+cudaError_t launch_beam_weight_digits(const float2* w, int8_t* dig, float* scale, int nchan, int nbeam, int ninput,
+                                      cudaStream_t stream);
+cudaError_t launch_beamform_tc(const BeamArgs& a, const int8_t* dig, const float* scale, int nsm, cudaStream_t stream);
+#ifdef __CUDACC__
+// [|X|^2, |Y|^2, Re X Y*, Im X Y*] of one sample (beamformer_sum_test.py:64-77).  Explicit fma/mul so that every
+// kernel forming these products (stand-alone integrate, both fused beamformer epilogues) rounds identically.
+__device__ __forceinline__ float4 beam_products(float2 x, float2 y) {
+  return make_float4(__fmaf_rn(x.y, x.y, __fmul_rn(x.x, x.x)), __fmaf_rn(y.y, y.y, __fmul_rn(y.x, y.x)),
+                     __fmaf_rn(x.y, y.y, __fmul_rn(x.x, y.x)), __fmaf_rn(x.y, y.x, -__fmul_rn(x.x, y.y)));
+}
+#endif
 cudaError_t launch_snap2_assemble(const uint8_t* pkts, int npkt, long pkt_stride, uint8_t* out, unsigned long long seq0,
                                   int ntime, int nchan, int ninput, int first_chan, int* nvalid, cudaStream_t stream);
 cudaError_t launch_beamform(const BeamArgs& a, cudaStream_t stream);

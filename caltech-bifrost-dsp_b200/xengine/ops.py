@@ -166,14 +166,24 @@ class Beamformer(object):
     def set_stream(self, stream):
         check(self._lib.xeng_bf_set_stream(self._h, ptr(stream)), "xeng_bf_set_stream")
 
-    def run(self, d_in, d_out, d_weights):
+    def run(self, d_in, d_out, d_weights=None):
+        """bfBeamformRun(in, out, weights).  d_weights=None: the weights last given to set_weights."""
         check(self._lib.xeng_bf_run(self._h, ptr(d_in), ptr(d_out), ptr(d_weights)), "xeng_bf_run")
+
+    def set_weights(self, d_weights):
+        """Convert cf32 [nchan][nbeam][ninput] weights to the tensor-core kernel's int8 digit planes once; later
+        run / run_integrate calls with d_weights=None use them.  The buffer must outlive its use."""
+        check(self._lib.xeng_bf_set_weights(self._h, ptr(d_weights)), "xeng_bf_set_weights")
+
+    def set_impl(self, impl):
+        """0: tcgen05 int8 kernel when the shape allows (default); 1: fp32 FMA kernel (cross-check)."""
+        check(self._lib.xeng_bf_set_impl(self._h, int(impl)), "xeng_bf_set_impl")
 
     def set_tap(self, on):
         """Keep the voltage beams of run_integrate in the handle (two kernels) instead of the fused power epilogue."""
         check(self._lib.xeng_bf_set_tap(self._h, int(bool(on))), "xeng_bf_set_tap")
 
-    def run_integrate(self, d_in, d_out, d_weights, ntime_sum):
+    def run_integrate(self, d_in, d_out, d_weights, ntime_sum):    # d_weights may be None (set_weights)
         """Beamform's ntime_sum mode: integrated powers go to d_out; one fused kernel for ntime_sum <= 128."""
         check(self._lib.xeng_bf_run_integrate(self._h, ptr(d_in), ptr(d_out), ptr(d_weights), int(ntime_sum)),
               "xeng_bf_run_integrate")

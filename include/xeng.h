@@ -154,6 +154,16 @@ int xeng_bf_set_stream(xeng_bf_t h, void* cuda_stream);
 /* Replaces bfBeamformRun(in, out, weights) -- beamform_block.py:449.
  * d_in u8 [ntime][nchan][ninput]; d_weights cf32 [nchan][nbeam][ninput]; d_out cf32 [nchan][nbeam][ntime]. */
 int xeng_bf_run(xeng_bf_t h, const void* d_in, void* d_out, const void* d_weights);
+/* Where bfBeamformRun receives the weights with every call (beamform_block.py:449), the tensor-core kernel reads
+ * them as int8 digit planes (24-bit block floating point per (channel, beam) row; csrc/xeng_beam_tc.cu).
+ * xeng_bf_run(..., d_weights != NULL) converts them on the stream before every launch (drop-in semantics: the
+ * caller may have rewritten the buffer, as Beamform does at beamform_block.py:431).  A caller that knows when its
+ * weights change converts once with xeng_bf_set_weights and then passes d_weights = NULL to xeng_bf_run /
+ * xeng_bf_run_integrate.  The d_weights buffer must stay valid until the next set_weights (the fp32 kernel reads it). */
+int xeng_bf_set_weights(xeng_bf_t h, const void* d_weights);
+/* 0 (default): tcgen05 int8 kernel whenever ninput % 16 == 0, ninput <= 2032 and d_in is 16-byte aligned, else the
+ * fp32 FMA kernel; 1: always the fp32 FMA kernel (independent cross-check, as xeng_corr_set_impl). */
+int xeng_bf_set_impl(xeng_bf_t h, int impl);
 /* Replaces bfBeamformIntegrate(in, out, ntime_sum) -- beamform_sum_beams_block.py:245, beamform_sum_block.py:116.
  * d_in cf32 [nchan][nbeam][ntime]; d_out f32 [nbeam/2][ntime/ntime_sum][nchan][4]. */
 int xeng_bf_integrate(xeng_bf_t h, const void* d_in, void* d_out, int ntime_sum);
