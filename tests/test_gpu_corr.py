@@ -378,3 +378,52 @@ def test_reorder_arbitrary_tables_take_the_general_path(torch_cuda):
     ops.reorder(torch.from_numpy(x).cuda(), full, torch.from_numpy(a2bl).cuda(), torch.from_numpy(conj).cuda(),
                 nstand, 2, nchan, wpc)
     assert np.array_equal(full.cpu().numpy(), orc.reorder(x, a2bl, conj))
+
+
+def test_config2_full_dump_every_channel_with_fused_fast_dump(torch_cuda):
+    """BASELINE configs[1]/[4] at full width, EVERY channel against the oracle ("bit-exact vs
+    oracle in xGPU order for >= 1 full dump at reduced length"): 704 inputs x 192 channels x 480-sample gulps,
+    10 spans accumulated by the fused Corr+CorrAcc+CorrSubsel launch.  Per span the fast dump (4704 baselines for the
+    first five spans, 4656 for the rest, nchan_sum = 4) equals orc.subselect(orc.corr_xgpu(span)); the long
+    accumulator equals the sum of the ten oracle matrices on all 2 x 192 x 249 216 words.  Voltages as the reference
+    generates them (make_golden_inputs.py:57,137: RandomState(0xdeadbeef).randint(0, 255)) plus the edge bytes that
+    randint(0, 255) never yields.  The persistent tile walk wraps channels across the 148 CTAs: only a run at the full
+    channel count visits every wrap."""
+    from xengine import ops
+    torch = torch_cuda
+    nt, nchan, nstand, nspan = 480, 192, 352, 10
+    wpc = ops.words_per_chan(nstand)
+    rs = np.random.RandomState(0xdeadbeef)
+    rng = np.random.default_rng(17)
+    a2bl, conj = ops.get_order(np.arange(nstand * 2, dtype=np.int32).reshape(nstand, 2))
+    # 4704 = 48 stands x 48 stands lower triangle x 4 pol products (corr_subsel_block.py:185), both station orders;
+    # 4656 (docs/source/outputs.rst:369) = random words
+    st = rng.choice(nstand, 48, replace=False)
+    bls_a = [[[int(s0), p0], [int(s1), p1]] for i, s0 in enumerate(st) for s1 in st[:i + 1]
+             for p0 in range(2) for p1 in range(2)]
+    assert len(bls_a) == 4704
+    bls_b = [[[int(rng.integers(nstand)), int(rng.integers(2))], [int(rng.integers(nstand)), int(rng.integers(2))]]
+             for _ in range(4656)]
+    sel = {4704: orc.baselines_to_vismap(bls_a, a2bl, conj), 4656: orc.baselines_to_vismap(bls_b, a2bl, conj)}
+    xc = ops.XCorr(nstand=nstand, nchan=nchan, ntime_gulp=nt)
+    acc = torch.full((2, nchan, wpc), 3, dtype=torch.int32, device="cuda")
+    want_acc = np.zeros((2, nchan, wpc), dtype=np.int64)
+    for g in range(nspan):
+        nvis = 4704 if g < 5 else 4656
+        vm, cj = sel[nvis]
+        if g in (0, 5):
+            xc.set_subsel(vm, cj, 4)
+            fast = torch.full((nchan // 4, nvis, 2), -9, dtype=torch.int32, device="cuda")
+        v = rs.randint(0, 255, size=(nt, nchan, nstand, 2), dtype=np.uint8)
+        flat = v.reshape(-1)
+        flat[:8] = [0xFF, 0x88, 0x80, 0x08, 0x00, 0x77, 0x78, 0x87]
+        flat[-4:] = [0x88, 0x88, 0xFF, 0x80]
+        xc.accumulate_subsel(torch.from_numpy(v).cuda(), acc, g == 0, fast)      # runs while the oracle computes
+        x = orc.corr_xgpu(v)
+        want_acc += x
+        xc.sync()
+        assert np.array_equal(fast.cpu().numpy(), orc.subselect(x, vm, cj, 4)), "fast dump of span %d" % g
+    got = acc.cpu().numpy()
+    assert np.array_equal(got, want_acc.astype(np.int32))
+    assert np.abs(want_acc).max() < 2 ** 31
+    xc.close()
