@@ -1,12 +1,18 @@
 #!/usr/bin/env python
 """X-engine benchmark (contract: see the task statement / DESIGN.md "Measurement").
 
-Workload (BASELINE.json configs[1]): Corr + CorrAcc on one B200 -- 704 inputs x 192 channels,
-480-sample gulps, accumulated to 250-gulp (~5 s of sky) dumps.  One step = one 480-sample gulp
-(64 880 640 4+4-bit complex samples per GPU) through the fused correlate+accumulate kernel; every
-`--acc-gulps` steps the integration is dumped (device copy for `value`, D2H to pinned memory for `e2e`).
-N > 1: every rank owns its own channel slab (weak scaling, no data-path collective); at each dump the
-accumulated visibilities are gathered to rank 0 over NCCL.
+N = 1 (BASELINE.json configs[1]): Corr + CorrAcc on one B200 -- 704 inputs x 192 channels, 480-sample gulps,
+accumulated to 250-gulp (~5 s of sky) dumps.  One step = one 480-sample gulp (64 880 640 4+4-bit complex samples)
+through the fused correlate+accumulate kernel; every `--acc-gulps` steps the integration is dumped (device copy for
+`value`, D2H to pinned memory for `e2e`).
+N > 1 (configs[2] + configs[4]): every rank owns a 384-channel slab of the 3072-channel band (weak scaling, no
+data-path collective).  One step = one 480-sample gulp through the fused correlate + accumulate + sub-select kernel;
+EVERY step the rank's fast dump (int32 [96][4704][2], 3.6 MB) is pushed to rank 0 by peer writes over NVLink inside
+the timed region (the exchange the reference makes as UDP packets every integration, corr_subsel_block.py:298-305);
+every `--acc-gulps` steps the 766 MB accumulated visibilities are gathered to rank 0 too.
+The same JSON line carries `xengine_full`: the whole X-engine (Corr+CorrAcc+CorrSubsel AND Beamform+power on the same
+gulps, two streams; N > 1: fast dumps and beam powers pushed to rank 0 every step) against the 51.74 Gsamples/s
+full-band real-time rate, and `blocks_graph`: the same work driven through the Python blocks on the ring shim.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 """
@@ -39,7 +45,8 @@ def parse():
     p.add_argument("--steps", type=int, default=250)
     p.add_argument("--warmup", type=int, default=10)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    p.add_argument("--nchan-per-gpu", type=int, default=192)
+    p.add_argument("--nchan-per-gpu", type=int, default=None,
+                   help="default: 192 at --gpus 1 (configs[1]), 384 at --gpus > 1 (3072 / 8, configs[2])")
     p.add_argument("--ntime", type=int, default=480)
     p.add_argument("--acc-gulps", type=int, default=250)
     p.add_argument("--nccl-gather", action="store_true",
@@ -47,7 +54,12 @@ def parse():
     p.add_argument("--cpu-seconds", type=float, default=15.0, help="budget for the cpu_baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-path-kernels", action="store_true", help="skip the per-kernel figures of the rest of the path")
-    return p.parse_args()
+    p.add_argument("--no-xengine-full", action="store_true", help="skip the whole-X-engine and block-graph sections")
+    p.add_argument("--full-steps", type=int, default=40, help="steps of the whole-X-engine section")
+    a = p.parse_args()
+    if a.nchan_per_gpu is None:
+        a.nchan_per_gpu = 192 if a.gpus == 1 else 384
+    return a
 
 
 def peaks():
@@ -62,18 +74,27 @@ def peaks():
 # ----------------------------------------------------------------------------------------------
 # CPU arm: the reference's own CPU formulation of the path (numpy; bifrost/xGPU are absent submodules)
 # ----------------------------------------------------------------------------------------------
-def cpu_corr_sample(nchan_total, ntime, budget_s, seed=0xdeadbeef, wrap=False):
+def cpu_corr_sample(nchan_total, ntime, budget_s, seed=0xdeadbeef, wrap=False, gulp=None):
     """Time oracle Corr (xGPU order) + CorrAcc on a bounded sample of the workload: a slab of channels of
     one gulp, grown until ~budget_s of CPU work has been spent (wrap=True carries on into further gulps when
-    the host finishes one gulp inside the budget).  Returns (Gsamples/s, description, cores)."""
+    the host finishes one gulp inside the budget).  `gulp`: uint8 [ntime][nchan][704], the GPU leg's own first gulp
+    ("same synthetic input"); without it (reference arm: no GPU in the process) bytes are drawn as the
+    reference's generator draws them (make_golden_inputs.py:137).  Returns (Gsamples/s, description, cores, s, samples)."""
     from oracle import xeng_oracle as orc
     rng = np.random.RandomState(seed & 0xFFFFFFFF)
     nch = 2
-    v = rng.randint(0, 255, size=(ntime, nch, NSTAND, NPOL), dtype=np.uint8)   # make_golden_inputs.py:137
-    orc.corr_xgpu(v)                                                           # warm-up (BLAS threads, index maps)
+
+    def slab(c):
+        if gulp is None:
+            return rng.randint(0, 255, size=(ntime, nch, NSTAND, NPOL), dtype=np.uint8)
+        c %= gulp.shape[1] - nch + 1
+        return np.ascontiguousarray(gulp[:, c:c + nch]).reshape(ntime, nch, NSTAND, NPOL)
+
+    orc.corr_xgpu(slab(0))                                                     # warm-up (BLAS threads, index maps)
     done_ch, t_used = 0, 0.0
     acc = None
     while t_used < budget_s and (wrap or done_ch < nchan_total):
+        v = slab(done_ch)
         t0 = time.perf_counter()
         x = orc.corr_xgpu(v)
         acc = orc.corr_acc(x.copy() if acc is None else acc, x, first=acc is None)
@@ -82,9 +103,43 @@ def cpu_corr_sample(nchan_total, ntime, budget_s, seed=0xdeadbeef, wrap=False):
     samples = done_ch * ntime * NINPUT
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     desc = "%d channels = %.2f gulps of %d channels x %d samples, 704 inputs (numpy/BLAS float32-exact matmul " \
-           "port of Corr._test + CorrAcc, all host threads), %.1f s" % (done_ch, done_ch / nchan_total, nchan_total,
-                                                                        ntime, t_used)
+           "port of Corr._test + CorrAcc, all host threads%s), %.1f s" % (
+               done_ch, done_ch / nchan_total, nchan_total, ntime,
+               ", the GPU leg's own voltages" if gulp is not None else "", t_used)
     return samples / t_used / 1e9, desc, cores, t_used, samples
+
+
+def cpu_literal_sample(gulp, nt_sub=96):
+    """The reference's literal verification loop (Corr._test, corr_block.py:279-284: four np.outer per (time, channel))
+    on a stated subset -- one channel x nt_sub samples of the GPU leg's first gulp -- on one core; checked equal to
+    the BLAS port on the same bytes."""
+    from oracle import xeng_oracle as orc
+    v = np.ascontiguousarray(gulp[:nt_sub, :1]).reshape(nt_sub, 1, NSTAND, NPOL)
+    t0 = time.perf_counter()
+    lit = orc.corr_loop_literal(v)
+    dt = time.perf_counter() - t0
+    fre, fim = orc.corr_full(v)                       # [chan, s0, s1, p0, p1] = sum v(s0,p0) conj(v(s1,p1))
+    same = True
+    for p0 in range(NPOL):
+        for p1 in range(NPOL):                        # literal: out[c, i, j, 2 p0 + p1] = sum conj(v(i,p0)) v(j,p1)
+            want = fre[:, :, :, p1, p0].transpose(0, 2, 1) + 1j * fim[:, :, :, p1, p0].transpose(0, 2, 1)
+            same = same and bool(np.array_equal(lit[:, :, :, 2 * p0 + p1], want))
+    return {"value": nt_sub * NINPUT / dt / 1e9, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": "literal np.outer loop of corr_block.py:279-284, 1 channel x %d samples x 704 inputs, %.2f s "
+                      "(a 480 x 192 gulp at this rate: %.0f s)" % (nt_sub, dt, dt / nt_sub * 480 * 192),
+            "equals_blas_port": same}
+
+
+def verify_accumulator(orc, d_acc, nchan, wpc, counts, gulps_host, chans):
+    """The timed accumulator against the oracle on the SAME bytes: channels `chans` of sum_k counts[k] X(gulp k)."""
+    import torch
+    got = d_acc.view(2, nchan, wpc)[:, chans].cpu().numpy()
+    want = np.zeros(got.shape, dtype=np.int64)
+    for k, n in enumerate(counts):
+        if n:
+            v = np.ascontiguousarray(gulps_host[k][:, chans]).reshape(-1, len(chans), NSTAND, NPOL)
+            want += int(n) * orc.corr_xgpu(v).astype(np.int64)
+    return bool(np.array_equal(got, want.astype(np.int32)))
 
 
 def run_reference(args):
@@ -116,12 +171,18 @@ def run_reference(args):
 
 def workload_config(args):
     return {
-        "workload": "Corr+CorrAcc: 704 inputs (352 stands x 2 pol) x %d channels/GPU, %d-sample gulps of 4+4-bit "
-                    "voltages, fused correlate+accumulate, dump every %d gulps" % (args.nchan_per_gpu, args.ntime,
-                                                                                 args.acc_gulps),
+        "workload": "Corr+CorrAcc%s: 704 inputs (352 stands x 2 pol) x %d channels/GPU, %d-sample gulps of 4+4-bit "
+                    "voltages, fused correlate+accumulate%s, dump every %d gulps" % (
+                        "+CorrSubsel (BASELINE configs[2]+[4])" if args.gpus > 1 else " (BASELINE configs[1])",
+                        args.nchan_per_gpu, args.ntime,
+                        "+sub-select with the fast dump shipped to rank 0 every step" if args.gpus > 1 else "",
+                        args.acc_gulps),
         "nchan_per_gpu": args.nchan_per_gpu, "ninput": NINPUT, "ntime_gulp": args.ntime,
         "acc_gulps": args.acc_gulps,
-        "sharding": "channel slabs, 1 rank per GPU over torch.distributed/NCCL, each dump gathered to rank 0 on a side stream (overlaps the next integration, inside the timed region)" if args.gpus > 1 else "single GPU",
+        "sharding": ("channel slabs of the 3072-channel band, 1 rank per GPU over torch.distributed/NCCL; EVERY step each "
+                     "rank's fast dump (CorrSubsel's 4704 baselines, fused into the correlator launch) is pushed to "
+                     "rank 0 over NVLink inside the timed region; each long dump is gathered to rank 0 on a side stream")
+                    if args.gpus > 1 else "single GPU",
         "l2": "inputs rotate over 4 distinct gulps (>=260 MB) and every step read-modify-writes the 383 MB "
               "accumulator, both larger than the 126 MB L2",
     }
@@ -334,10 +395,27 @@ def path_kernels(torch, ops, dev, nchan, hbm_peak, iters=10):
 # ----------------------------------------------------------------------------------------------
 # B200 arm
 # ----------------------------------------------------------------------------------------------
+def stats(x):
+    x = np.asarray(x, dtype=np.float64)
+    return {"min": float(x.min()), "median": float(np.median(x)), "max": float(x.max())}
+
+
+def real_selection(ops, orc, rng, nvis_stands=48):
+    """CorrSubsel's selection shape (corr_subsel_block.py:185: 48 x 49 / 2 stand pairs x 4 pol products = 4704) for
+    48 random stands: whole 16-byte cells, both station orders."""
+    a2bl, conj = ops.get_order(np.arange(NINPUT, dtype=np.int32).reshape(NSTAND, NPOL))
+    st = rng.choice(NSTAND, nvis_stands, replace=False)
+    bls = [[[int(s0), p0], [int(s1), p1]] for i, s0 in enumerate(st) for s1 in st[:i + 1]
+           for p0 in range(2) for p1 in range(2)]
+    vm, cj = orc.baselines_to_vismap(bls, a2bl, conj)
+    return vm, cj
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
     from xengine import ops, sharding
+    from oracle import xeng_oracle as orc          # the checker: verification of what was timed + the CPU leg
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the B200 arm has no CPU fallback (use --impl reference)")
@@ -359,6 +437,8 @@ def run_b200(args):
     nsamp_step = ntime * nchan * NINPUT                      # per GPU
     in_bytes = nsamp_step
     out_words = 2 * nchan * wpc
+    fused_fast = world > 1                                   # N > 1: the step also produces + ships the fast dump
+    NVIS, NSUM = 4704, 4
 
     # synthetic voltages: 4 distinct gulps, uniform bytes, fixed seed (per rank = per channel slab)
     g = torch.Generator(device=dev)
@@ -366,37 +446,49 @@ def run_b200(args):
     NBUF = 4
     d_in = [torch.randint(0, 256, (ntime, nchan, NINPUT), dtype=torch.uint8, device=dev, generator=g)
             for _ in range(NBUF)]
+    gulps_host = [x.cpu().numpy() for x in d_in]
     d_acc = torch.zeros(out_words, dtype=torch.int32, device=dev)
     d_dump = torch.zeros(out_words, dtype=torch.int32, device=dev)
     gather_list = None
     stream = torch.cuda.Stream(device=dev)
     xc = ops.XCorr(nstand=NSTAND, npol=NPOL, nchan=nchan, ntime_gulp=ntime, gpu=local)
     xc.set_stream(stream)
+    vm, cj = real_selection(ops, orc, np.random.default_rng(4704))
+    xc.set_subsel(vm, cj, NSUM)
+    fast = [torch.zeros((nchan // NSUM, NVIS, 2), dtype=torch.int32, device=dev) for _ in range(2)]
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    gstream = torch.cuda.Stream(device=dev) if world > 1 else None
-    peer = None
-    if world > 1 and not args.nccl_gather:
-        try:
-            peer = sharding.PeerGather(out_words, torch.int32, dev, dist, root=0)
-        except Exception as e:                              # no symmetric memory on this node: all ranks use NCCL
-            sys.stderr.write("rank %d: PeerGather unavailable (%s)\n" % (rank, e))
-        agreed = torch.tensor([1 if peer is not None else 0], device=dev)
+    # ---- exchanges (N > 1): long dump -> PeerGather, per-step fast dump -> PeerStream; NCCL fallbacks
+    gstream = torch.cuda.Stream(device=dev) if world > 1 else None      # long dumps
+    pstream = torch.cuda.Stream(device=dev) if world > 1 else None      # per-step pushes
+    peer = fpush = None
+    push_kind = None
+    if world > 1:
+        if not args.nccl_gather:
+            try:
+                peer = sharding.PeerGather(out_words, torch.int32, dev, dist, root=0)
+                fpush = sharding.PeerStream(fast[0].numel(), torch.int32, dev, dist, nslot=2, root=0)
+            except Exception as e:                              # no symmetric memory on this node: all ranks use NCCL
+                sys.stderr.write("rank %d: symmetric-memory peer writes unavailable (%s)\n" % (rank, e))
+                peer = fpush = None
+        agreed = torch.tensor([1 if (peer is not None and fpush is not None) else 0], device=dev)
         dist.all_reduce(agreed, op=dist.ReduceOp.MIN)
         if int(agreed) == 0:
             peer, args.nccl_gather = None, True
+            fpush = sharding.GatherStream(fast[0].numel(), torch.int32, dev, dist, nslot=2, root=0)
+            push_kind = "NCCL dist.gather every step"
         else:
             d_dump = peer.slot if rank == 0 else d_dump    # rank 0 snapshots straight into its own slot
-
+            push_kind = "peer writes into rank 0's symmetric-memory slots (copy engines over NVLink), no cross-rank wait"
     if world > 1 and rank == 0 and args.nccl_gather:
         gather_list = [d_dump] + [torch.empty_like(d_dump) for _ in range(world - 1)]
 
     def dump_device():
-        # CorrAcc's copy_array into its output span, then (N > 1) the NCCL gather of that span to rank 0 on a side
+        # CorrAcc's copy_array into its output span, then (N > 1) the gather of that span to rank 0 on a side
         # stream: as in the pipeline, the correlator carries on with the next integration while the previous dump
         # travels; the next dump waits for it, and so does the end of the timed region.
         if world > 1:
@@ -410,46 +502,87 @@ def run_b200(args):
                 else:
                     sharding.gather_to_root(d_dump, dist, root=0, out=gather_list)
 
-    def step_device(i):
-        xc.accumulate(d_in[i % NBUF], d_acc, (i % accg) == 0)
-        if (i % accg) == accg - 1:
-            dump_device()
+    fast_done = [torch.cuda.Event() for _ in range(2)]
+    fast_free = [torch.cuda.Event() for _ in range(2)]
+    counts = [0] * NBUF                                      # gulps of each buffer in the running integration
+    nlaunch = [0]
+    seqc = [0]
+
+    def launch_step(src, k_buf, first):
+        """One step on `stream` (current): the hot-path launch (+ N > 1: the fast dump's push on the side stream).
+        Returns the step's sequence number."""
+        seq = seqc[0]
+        seqc[0] += 1
+        if first:
+            for k in range(NBUF):
+                counts[k] = 0
+        counts[k_buf] += 1
+        if not fused_fast:
+            xc.accumulate(src, d_acc, first)
+            nlaunch[0] += 1
+            return seq
+        slot = seq % 2
+        stream.wait_event(fast_free[slot])                   # the push of step seq - 2 has left this buffer
+        xc.accumulate_subsel(src, d_acc, first, fast[slot], True)
+        nlaunch[0] += 1
+        fast_done[slot].record(stream)
+        with torch.cuda.stream(pstream):
+            pstream.wait_event(fast_done[slot])
+            fpush.push(fast[slot], seq)
+            fast_free[slot].record(pstream)
+        return seq
 
     # ---- value: inputs resident in HBM
     with torch.cuda.stream(stream):
         for i in range(Wm):
-            step_device(i)
+            launch_step(d_in[i % NBUF], i % NBUF, (i % accg) == 0)
         dump_device()          # warm the dump path too (first NCCL gather sets up its peer connections)
+        # open a fresh integration (untimed) so that the accumulator the timed region leaves behind is a known sum
+        launch_step(d_in[NBUF - 1], NBUF - 1, True)
     barrier()
     sampler = ClockSampler(local) if rank == 0 else None
     evs = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
     ndump = 0
     phase = accg // 2
+    last_seq = -1
     with torch.cuda.stream(stream):
         # the timed region starts in the middle of a long integration (steady state): a dump falls every `accg`
         # steps, the first after accg - accg // 2, and travels to rank 0 while the next integration runs
         evs[0].record(stream)
         for i in range(K):
             g_i = i + phase
-            xc.accumulate(d_in[i % NBUF], d_acc, (g_i % accg) == 0)
+            last_seq = launch_step(d_in[i % NBUF], i % NBUF, (g_i % accg) == 0)
             evs[i + 1].record(stream)
             if (g_i % accg) == accg - 1:
                 dump_device()
                 ndump += 1
         if world > 1:
             stream.wait_stream(gstream)
+            stream.wait_stream(pstream)
         end = torch.cuda.Event(enable_timing=True)
         end.record(stream)
     barrier()
     total_ms = evs[0].elapsed_time(end)
-    # kernel-only time: intervals that contain exactly one corr kernel (those after a dump also contain the copy)
-    kern = []
-    for i in range(K):
-        prev_dump = i > 0 and (((i - 1 + phase) % accg) == accg - 1)
-        if not prev_dump:
-            kern.append(evs[i].elapsed_time(evs[i + 1]))
-    kern_ms = float(np.mean(kern)) if kern else total_ms / K
+    step_ms = [evs[i].elapsed_time(evs[i + 1]) for i in range(K)]
+    # kernel-only time: intervals that contain exactly one hot-path launch (those after a dump also contain the copy)
+    kern = [step_ms[i] for i in range(K) if not (i > 0 and (((i - 1 + phase) % accg) == accg - 1))]
+    kern_ms = float(np.median(kern)) if kern else total_ms / K
     xc.sync()
+    # what was timed is what the reference computes: two channel slabs of the accumulator the timed region left
+    # behind against the oracle on the same bytes
+    vchans = [0, nchan // 2 - 1] if nchan > 2 else [0]
+    verified = verify_accumulator(orc, d_acc, nchan, wpc, counts, gulps_host, vchans)
+    fast_verified = None
+    if fused_fast:                                           # and the last fast dump, every channel group
+        last = last_seq
+        x_last = None
+        sub_ch = [0, 1, 2, 3]                                # first output channel = input channels 0..3
+        v4 = np.ascontiguousarray(gulps_host[(K - 1) % NBUF][:, sub_ch]).reshape(ntime, 4, NSTAND, NPOL)
+        x_last = orc.corr_xgpu(v4)
+        fast_verified = bool(np.array_equal(fast[last % 2][0].cpu().numpy(), orc.subselect(x_last, vm, cj, NSUM)[0]))
+    if not verified or fast_verified is False:
+        raise RuntimeError("timed accumulator / fast dump differ from the oracle on the same voltages")
+
     # one dump on its own (copy + gather, nothing to overlap with): what each long integration adds at most
     barrier()
     with torch.cuda.stream(stream):
@@ -462,18 +595,28 @@ def run_b200(args):
         dmp1.record(stream)
     barrier()
     dump_ms = dmp0.elapsed_time(dmp1)
-    gather_ok = None
+    gather_ok = push_ok = None
     if world > 1:                                           # what arrived on rank 0 is what each rank sent
-        probe = torch.stack([d_dump[:4096].to(torch.int64).sum(), d_dump[-4096:].to(torch.int64).sum()])
+        with torch.cuda.stream(pstream):
+            fpush.finish()
+        torch.cuda.synchronize(dev)
+        last = last_seq
+        probe = torch.stack([d_dump[:4096].to(torch.int64).sum(), d_dump[-4096:].to(torch.int64).sum(),
+                             fast[last % 2].to(torch.int64).sum(), fast[last % 2][-1].to(torch.int64).sum()])
         sent = [torch.empty_like(probe) for _ in range(world)]
         dist.all_gather(sent, probe)
         if rank == 0:
             got = peer.parts() if peer is not None else gather_list
             gather_ok = all(bool((torch.stack([got[r][:4096].to(torch.int64).sum(),
-                                               got[r][-4096:].to(torch.int64).sum()]) == sent[r]).all())
+                                               got[r][-4096:].to(torch.int64).sum()]) == sent[r][:2]).all())
                             for r in range(world))
-            if not gather_ok:
-                raise RuntimeError("gathered dump on rank 0 differs from what the ranks sent")
+            payload, seqs = fpush.slot_on_root(last)
+            payload = payload.view(world, nchan // NSUM, NVIS, 2)
+            push_ok = bool((seqs == last).all()) and all(
+                bool((torch.stack([payload[r].to(torch.int64).sum(), payload[r][-1].to(torch.int64).sum()])
+                      == sent[r][2:]).all()) for r in range(world))
+            if not gather_ok or not push_ok:
+                raise RuntimeError("dump / fast dumps on rank 0 differ from what the ranks sent")
 
     # ---- e2e: host (pinned) voltages in, dump to pinned host memory out, copies inside the timed region
     h_in = [torch.empty((ntime, nchan, NINPUT), dtype=torch.uint8).pin_memory() for _ in range(2)]
@@ -484,6 +627,18 @@ def run_b200(args):
     copy_stream = torch.cuda.Stream(device=dev)
     filled = [torch.cuda.Event() for _ in ring]
     freed = [torch.cuda.Event() for _ in ring]
+
+    # the PCIe ceiling, on the record: plain pinned cudaMemcpyAsync H2D of the same gulp, nothing else running
+    barrier()
+    with torch.cuda.stream(copy_stream):
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ring[0].copy_(h_in[0], non_blocking=True)
+        p0.record(copy_stream)
+        for j in range(8):
+            ring[j % 3].copy_(h_in[j % 2], non_blocking=True)
+        p1.record(copy_stream)
+    barrier()
+    h2d_probe_gbs = 8 * in_bytes / p0.elapsed_time(p1) / 1e6
 
     def e2e_steps(n, first_index):
         d2h = 0
@@ -496,34 +651,64 @@ def run_b200(args):
                 filled[slot].record(copy_stream)
             with torch.cuda.stream(stream):
                 stream.wait_event(filled[slot])
-                xc.accumulate(ring[slot], d_acc, (i % accg) == 0)
+                launch_step(ring[slot], i % 2, (i % accg) == 0)
                 freed[slot].record(stream)
                 if (i % accg) == accg - 1 or j == n - 1:
                     h_out.copy_(d_acc, non_blocking=True)      # CorrAcc dump into a cuda_host ring span
                     d2h += out_words * 4
         return d2h
 
-    for s in range(len(ring)):
-        freed[s].record(stream)
-    e2e_steps(min(Wm, 6), 0)
+    for s_ in range(len(ring)):
+        freed[s_].record(stream)
+    n_e2e_warm = max(1, min(Wm, 6))
+    e2e_steps(n_e2e_warm, 0)                                   # i = 0 opens a fresh integration
     barrier()
     t0 = torch.cuda.Event(enable_timing=True)
     t1 = torch.cuda.Event(enable_timing=True)
     t0.record(stream)
     copy_stream.wait_event(t0)
-    d2h_total = e2e_steps(K, 0)
+    d2h_total = e2e_steps(K, n_e2e_warm)
     stream.wait_stream(copy_stream)
+    if world > 1:
+        stream.wait_stream(pstream)
     t1.record(stream)
     barrier()
     e2e_ms = t0.elapsed_time(t1)
     clocks = sampler.stop() if sampler else None
-    checksum = int(h_out[:1024].to(torch.int64).sum())        # the device->host result is really read
+    # the device->host result is really read, and it is the right one (same bytes through the H2D ring)
+    h_acc = h_out.numpy().reshape(2, nchan, wpc)
+    want = np.zeros((2, len(vchans), wpc), dtype=np.int64)
+    for k in range(2):
+        if counts[k]:
+            v = np.ascontiguousarray(gulps_host[k][:, vchans]).reshape(ntime, len(vchans), NSTAND, NPOL)
+            want += counts[k] * orc.corr_xgpu(v).astype(np.int64)
+    e2e_verified = bool(np.array_equal(h_acc[:, vchans], want.astype(np.int32)))
+    if not e2e_verified:
+        raise RuntimeError("e2e dump (pinned host) differs from the oracle on the same voltages")
+    checksum = int(h_out[:1024].to(torch.int64).sum())
 
-    # ---- max over ranks
+    # ---- whole X-engine (row N1) on the same process group
+    full = None
+    if not args.no_xengine_full:
+        full = xengine_full(torch, dist, ops, sharding, orc, args, dev, world, rank, xc, d_in, gulps_host, d_acc, fast,
+                            vm, cj, stream, h_in, barrier)
+
+    # ---- max over ranks (+ every rank's own per-step figures on rank 0)
+    amort_ms = 0.0 if ndump > 0 else dump_ms * K / accg      # no long dump fell in the timed region: charge its share
+    per_rank = None
     if world > 1:
-        t = torch.tensor([total_ms, e2e_ms, kern_ms, dump_ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms, e2e_ms, kern_ms, dump_ms = [float(x) for x in t.tolist()]
+        t = torch.tensor([total_ms, e2e_ms, kern_ms, dump_ms, h2d_probe_gbs], dtype=torch.float64, device=dev)
+        allt = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(allt, t)
+        sv = torch.tensor(step_ms, dtype=torch.float64, device=dev)
+        allsv = [torch.empty_like(sv) for _ in range(world)]
+        dist.all_gather(allsv, sv)
+        per_rank = [{"rank": r, "total_ms": float(allt[r][0]), "e2e_ms": float(allt[r][1]),
+                     "step_ms": stats(allsv[r].cpu().numpy()), "h2d_probe_gbs": float(allt[r][4]),
+                     "e2e_h2d_gbs": in_bytes * K / float(allt[r][1]) / 1e6} for r in range(world)]
+        m = torch.stack(allt).max(dim=0).values
+        total_ms, e2e_ms, kern_ms, dump_ms = [float(x) for x in m[:4].tolist()]
+        amort_ms = 0.0 if ndump > 0 else dump_ms * K / accg
 
     if rank == 0:
         hbm_peak, peak_src = peaks()
@@ -548,30 +733,49 @@ def run_b200(args):
         except Exception:
             pass
         alg_bytes = in_bytes + 2 * out_words * 4                      # read gulp + read-modify-write accumulator
+        if fused_fast:
+            alg_bytes += 2 * fast[0].numel() * 4                      # fast dump zeroed + written
         traffic, traffic_src = ncu_traffic(nchan, ntime)
         achieved = alg_bytes / kern_ms / 1e6
         useful_tops = OPS_PER_SAMPLE * nsamp_step / kern_ms / 1e9
-        value = world * nsamp_step * K / total_ms / 1e6
+        eff_ms = total_ms + amort_ms
+        value = world * nsamp_step * K / eff_ms / 1e6
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
-            "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": eff_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int8->int32", "data": "synthetic",
             "config": workload_config(args),
             "clocks": clocks,
+            "verified": {"accumulator_vs_oracle_same_bytes": verified, "channels": vchans,
+                         "fast_dump_vs_oracle": fast_verified, "e2e_dump_vs_oracle": e2e_verified,
+                         "how": "after the timed region the accumulator it left behind (and the pinned-host dump of "
+                                "the e2e run) is compared word for word with oracle corr_xgpu + corr_acc on the same "
+                                "voltages, on these channels"},
             "e2e": {"value": world * nsamp_step * K / e2e_ms / 1e6, "unit": UNIT,
                     "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": d2h_total / K,
-                    "ms_per_step": e2e_ms / K, "checksum": checksum},
+                    "ms_per_step": e2e_ms / K, "checksum": checksum,
+                    "h2d_gbs_achieved_per_gpu": in_bytes * K / e2e_ms / 1e6,
+                    "h2d_probe_gbs": h2d_probe_gbs,
+                    "note": "h2d_probe_gbs = plain pinned cudaMemcpyAsync of the same gulp with nothing else running "
+                            "(the PCIe ceiling of this box); the e2e rate is input bytes / time, 1 B per sample"},
             "gpu_launches": K,
+            "gpu_launches_whole_run": nlaunch[0],
+            "step_ms": stats(step_ms),
             "dump": {"in_timed_region": ndump, "every_steps": accg, "alone_ms": dump_ms, "gather_verified": gather_ok,
+                     "amortised_ms_added_per_step": amort_ms / K,
                      "gather": None if world == 1 else ("NCCL dist.gather" if args.nccl_gather else
                                                         "peer writes into rank 0's symmetric-memory buffer (copy engines over NVLink)"),
                      "bytes_to_rank0": (world - 1) * out_words * 4,
                      "note": "dumps fall at their true cadence (every acc_gulps steps); alone_ms is one dump "
-                             "(device copy + gather to rank 0) timed with nothing to overlap"},
-            "roofline": {"kernel": "corr_swz_kernel (fused Corr+CorrAcc)", "bound": "hbm", "achieved": achieved,
+                             "(device copy + gather to rank 0) timed with nothing to overlap; when no dump falls "
+                             "inside the timed region its share alone_ms * steps / acc_gulps is ADDED to the timed "
+                             "total (no overlap assumed) before value and ms_per_step are formed"},
+            "roofline": {"kernel": "corr_swz_kernel (fused Corr+CorrAcc%s)" % ("+CorrSubsel" if fused_fast else ""),
+                         "bound": "hbm", "achieved": achieved,
                          "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
                          "traffic_source": traffic_src,
                          "peak_source": peak_src, "alg_bytes_per_launch": alg_bytes, "kernel_ms": kern_ms,
+                         "kernel_ms_is": "median over the timed steps of the CUDA-event interval around one launch",
                          "tensor": {"useful_int8_tops": useful_tops, "nominal_peak_tops": INT8_NOMINAL_TOPS,
                                     "frac_nominal": useful_tops / INT8_NOMINAL_TOPS,
                                     "measured_int8_gemm_tops": int8_meas,
@@ -579,18 +783,178 @@ def run_b200(args):
             "realtime": {"required_gsps_per_%dch" % nchan: nchan * NINPUT * 23925.78125 / 1e9,
                          "full_band_required_gsps": 3072 * NINPUT * 23925.78125 / 1e9},
         }
+        if world > 1:
+            line["fast_dump_push"] = {"every_step": True, "bytes_per_rank_per_step": fast[0].numel() * 4,
+                                      "how": push_kind, "verified_on_rank0": push_ok, "in_timed_region": K}
+            line["per_rank"] = per_rank
+        if full is not None:
+            line["xengine_full"] = full
         if not args.no_path_kernels and world == 1:
             del d_in, d_dump, ring
             torch.cuda.empty_cache()
             line["path_kernels"] = path_kernels(torch, ops, dev, nchan, hbm_peak)
+        if not args.no_xengine_full and world == 1:
+            try:
+                line["blocks_graph"] = blocks_graph(torch, nchan)
+            except Exception as e:                                      # a diagnostic section must not sink the line
+                line["blocks_graph"] = {"error": repr(e)}
         if not args.no_cpu_baseline:
-            v, desc, cores, _, _ = cpu_corr_sample(nchan * world, ntime, args.cpu_seconds, wrap=True)
+            v, desc, cores, _, _ = cpu_corr_sample(nchan * world, ntime, args.cpu_seconds, wrap=True, gulp=gulps_host[0])
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
+            line["cpu_baseline_literal"] = cpu_literal_sample(gulps_host[0])
         real_stdout.write(json.dumps(line) + "\n")
         real_stdout.flush()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def xengine_full(torch, dist, ops, sharding, orc, args, dev, world, rank, xc, d_in, gulps_host, d_acc, fast, vm, cj,
+                 stream, h_in, barrier):
+    """Row N1: the WHOLE X-engine on every GPU -- per 480-sample gulp, fused Corr+CorrAcc+CorrSubsel on one stream and
+    Beamform + power integration (32 beams, ntime_sum = 24, tensor-core kernel, weights pre-loaded) on the same bytes
+    on a second stream, as production runs Corr and Beamform off the same gpu-input ring
+    (lwa352-pipeline.py:232-234, 279-285).  N > 1: both per-step products (fast dump, beam powers) are pushed to rank 0.
+    Timed device-resident and end to end (pinned host gulps through a 3-slot H2D ring shared by both consumers)."""
+    nchan, ntime, K = args.nchan_per_gpu, args.ntime, args.full_steps
+    nbeam, nsum = 32, 24
+    nsamp = ntime * nchan * NINPUT
+    bstream = torch.cuda.Stream(device=dev)
+    bf = ops.Beamformer(gpu=dev.index, ninput=NINPUT, nchan=nchan, ntime=ntime, nbeam=nbeam)
+    bf.set_stream(bstream)
+    gw = torch.Generator(device=dev)
+    gw.manual_seed(7 + rank)
+    w = torch.randn((nchan, nbeam, NINPUT, 2), dtype=torch.float32, device=dev, generator=gw)
+    with torch.cuda.stream(bstream):
+        bf.set_weights(w)
+    pw = [torch.zeros((nbeam // 2, ntime // nsum, nchan, 4), dtype=torch.float32, device=dev) for _ in range(2)]
+    fpush = ppush = None
+    pstream = torch.cuda.Stream(device=dev)
+    if world > 1:
+        try:
+            fpush = sharding.PeerStream(fast[0].numel(), torch.int32, dev, dist, nslot=2, root=0)
+            ppush = sharding.PeerStream(pw[0].numel(), torch.float32, dev, dist, nslot=2, root=0)
+            ok = 1
+        except Exception:
+            ok = 0
+        agreed = torch.tensor([ok], device=dev)
+        dist.all_reduce(agreed, op=dist.ReduceOp.MIN)
+        if int(agreed) == 0:
+            fpush = sharding.GatherStream(fast[0].numel(), torch.int32, dev, dist, nslot=2, root=0)
+            ppush = sharding.GatherStream(pw[0].numel(), torch.float32, dev, dist, nslot=2, root=0)
+    a_done = [torch.cuda.Event() for _ in range(2)]
+    b_done = [torch.cuda.Event() for _ in range(2)]
+    slot_free = [torch.cuda.Event() for _ in range(2)]
+    nlaunch = [0]
+
+    def step(src, seq, first):
+        s = seq % 2
+        stream.wait_event(slot_free[s])
+        bstream.wait_event(slot_free[s])
+        with torch.cuda.stream(stream):
+            xc.accumulate_subsel(src, d_acc, first, fast[s], True)
+            a_done[s].record(stream)
+        with torch.cuda.stream(bstream):
+            bf.run_integrate(src, pw[s], None, nsum)
+            b_done[s].record(bstream)
+        nlaunch[0] += 2
+        with torch.cuda.stream(pstream):
+            pstream.wait_event(a_done[s])
+            if fpush is not None:
+                fpush.push(fast[s], seq)
+            pstream.wait_event(b_done[s])
+            if ppush is not None:
+                ppush.push(pw[s], seq)
+            slot_free[s].record(pstream)
+
+    def run(n, srcs, e2e, reset):
+        ring = filled = freed = copy_stream = None
+        if e2e:
+            ring = [torch.empty_like(d_in[0]) for _ in range(3)]
+            copy_stream = torch.cuda.Stream(device=dev)
+            filled = [torch.cuda.Event() for _ in ring]
+            freed = [torch.cuda.Event() for _ in ring]
+        barrier()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record(stream)
+        bstream.wait_event(t0)
+        if e2e:
+            copy_stream.wait_event(t0)
+        for i in range(n):
+            if e2e:
+                r = i % 3
+                with torch.cuda.stream(copy_stream):
+                    copy_stream.wait_event(freed[r])
+                    ring[r].copy_(srcs[i % len(srcs)], non_blocking=True)
+                    filled[r].record(copy_stream)
+                stream.wait_event(filled[r])
+                bstream.wait_event(filled[r])
+                step(ring[r], i, reset and i == 0)
+                with torch.cuda.stream(pstream):            # both consumers are done with the ring slot
+                    freed[r].record(pstream)
+            else:
+                step(srcs[i % len(srcs)], i, reset and i == 0)
+        stream.wait_stream(bstream)
+        stream.wait_stream(pstream)
+        t1.record(stream)
+        barrier()
+        return t0.elapsed_time(t1)
+
+    run(4, d_in, False, True)                                # warm-up (both kernels, the pushes); opens an integration
+    dev_ms = run(K, d_in, False, False)
+    # parity of what was just timed: the last step's fast dump (first output channel) and beam powers (two channels)
+    last = K - 1
+    v4 = np.ascontiguousarray(gulps_host[last % len(d_in)][:, :4]).reshape(ntime, 4, NSTAND, NPOL)
+    ok_fast = bool(np.array_equal(fast[last % 2][0].cpu().numpy(), orc.subselect(orc.corr_xgpu(v4), vm, cj, 4)[0]))
+    vb = np.ascontiguousarray(gulps_host[last % len(d_in)][:, :2])
+    wb = w[:2].cpu().numpy()
+    wantp = orc.beam_power_sum(orc.beamform(vb, wb[..., 0] + 1j * wb[..., 1]), nsum)
+    gotp = pw[last % 2][:, :, :2].cpu().numpy()
+    ok_pow = bool(np.abs(gotp - wantp).max() / np.abs(wantp).max() <= 1e-5)
+    if not ok_fast or not ok_pow:
+        raise RuntimeError("xengine_full: fast dump / beam powers differ from the oracle (%s, %s)" % (ok_fast, ok_pow))
+    run(3, h_in, True, True)
+    e2e_ms = run(K, h_in, True, False)
+    pushed_ok = None
+    if world > 1:
+        with torch.cuda.stream(pstream):
+            fpush.finish()
+        torch.cuda.synchronize(dev)
+        probe = torch.stack([fast[last % 2].to(torch.float64).sum(), pw[last % 2].to(torch.float64).sum()])
+        sent = [torch.empty_like(probe) for _ in range(world)]
+        dist.all_gather(sent, probe)
+        if rank == 0:
+            pf, sf = fpush.slot_on_root(last)
+            pp, sp = ppush.slot_on_root(last)
+            pushed_ok = bool((sf == last).all()) and bool((sp == last).all()) and all(
+                float(pf[r].to(torch.float64).sum()) == float(sent[r][0]) and
+                float(pp[r].to(torch.float64).sum()) == float(sent[r][1]) for r in range(world))
+        t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms, e2e_ms = float(t[0]), float(t[1])
+    bf.close()
+    full_band = 3072 * NINPUT * 23925.78125 / 1e9
+    val = world * nsamp * K / dev_ms / 1e6
+    e2e = world * nsamp * K / e2e_ms / 1e6
+    return {
+        "workload": "per step (one %d-sample gulp of %d channels x 704 inputs per GPU): fused Corr+CorrAcc+CorrSubsel "
+                    "(4704 baselines, nchan_sum 4) and Beamform+power (32 beams, ntime_sum 24, weights pre-loaded) on "
+                    "the same bytes, two streams%s" % (ntime, nchan, "; fast dump + beam powers pushed to rank 0 "
+                                                       "every step" if world > 1 else ""),
+        "steps": K, "ms_per_step": dev_ms / K, "gsamples_per_s": val, "per_gpu_gsamples_per_s": val / world,
+        "e2e_ms_per_step": e2e_ms / K, "e2e_gsamples_per_s": e2e, "gpu_launches": nlaunch[0],
+        "full_band_required_gsps": full_band, "x_realtime_full_band": val / full_band,
+        "e2e_x_realtime_full_band": e2e / full_band,
+        "verified": {"fast_dump_vs_oracle": ok_fast, "beam_powers_vs_oracle_1e-5": ok_pow, "pushes_on_rank0": pushed_ok},
+        "push_bytes_per_rank_per_step": (fast[0].numel() * 4 + pw[0].numel() * 4) if world > 1 else 0,
+    }
+
+
+def blocks_graph(torch, nchan):
+    """The same work driven through the Python blocks on the ring shim (tests/test_gpu_blocks.py's graph at full width):
+    source -> Corr(acc_len = 480, slow_acc_len, fast dump) and Beamform(ntime_sum) on one input ring."""
+    from xengine import blockbench
+    return blockbench.run(nchan=nchan)
 
 
 def main():

@@ -82,6 +82,77 @@ class PeerGather(object):
         return [self.buf[r * self.n:(r + 1) * self.n] for r in range(self.world)]
 
 
+class PeerStream(object):
+    """The frequent exchanges of the path -- CorrSubsel's fast dump every integration (corr_subsel_block.py:298-305)
+    and BeamformSum's powers every gulp (beamform_sum_beams_block.py:245-247), which the reference sends as UDP
+    packets to a central receiver -- as a stream of peer writes to ``root``: ``root`` owns ``nslot`` x [world][n]
+    slots in torch symmetric memory plus one sequence word per (slot, rank); ``push(src, seq)`` stores this rank's
+    product of step ``seq`` into slot ``seq % nslot`` with one device-to-device copy and then its sequence number
+    with a second, both on the current stream (copy engines over NVLink, in order; no SMs, no cross-rank wait: the
+    producer never blocks on the consumer).  A consumer on root that sees ``seq`` in the word knows the payload
+    before it has landed.  ``finish()`` is the one barrier, at the end of a run."""
+
+    def __init__(self, n, dtype, device, dist, nslot=2, root=0, max_seq=1 << 16):
+        import torch
+        import torch.distributed._symmetric_memory as symm_mem
+        self.dist, self.root, self.n, self.nslot = dist, root, n, nslot
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        self.buf = symm_mem.empty(nslot * self.world * n, dtype=dtype, device=device)
+        self.seqbuf = symm_mem.empty(nslot * self.world, dtype=torch.int64, device=device)
+        self.seqbuf.fill_(-1)
+        self.hdl = symm_mem.rendezvous(self.buf, dist.group.WORLD.group_name)
+        self.seq_hdl = symm_mem.rendezvous(self.seqbuf, dist.group.WORLD.group_name)
+        self.root_buf = self.hdl.get_buffer(root, (nslot, self.world, n), dtype)
+        self.root_seq = self.seq_hdl.get_buffer(root, (nslot, self.world), torch.int64)
+        self.numbers = torch.arange(max_seq, dtype=torch.int64, device=device)    # sources of the sequence words
+
+    def push(self, src, seq):
+        slot = seq % self.nslot
+        self.root_buf[slot, self.rank].copy_(src.reshape(-1), non_blocking=True)
+        self.root_seq[slot, self.rank].copy_(self.numbers[seq % self.numbers.numel()], non_blocking=True)
+
+    def finish(self):
+        self.hdl.barrier(channel=0)
+
+    def slot_on_root(self, seq):
+        """(payload [world][n], sequence words [world]) of step ``seq`` as root holds them (root only)."""
+        if self.rank != self.root:
+            return None, None
+        slot = seq % self.nslot
+        return (self.buf.view(self.nslot, self.world, self.n)[slot], self.seqbuf.view(self.nslot, self.world)[slot])
+
+
+class GatherStream(object):
+    """Portable form of ``PeerStream`` (any torch.distributed backend: NCCL without symmetric memory, gloo in the CPU
+    tests): every ``push`` is one ``dist.gather`` into root's slot ``seq % nslot``.  Collective: every rank must call
+    ``push`` for every step, in the same order."""
+
+    def __init__(self, n, dtype, device, dist, nslot=2, root=0):
+        import torch
+        self.dist, self.root, self.n, self.nslot = dist, root, n, nslot
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        self.buf = self.seqbuf = None
+        if self.rank == root:
+            self.buf = torch.zeros((nslot, self.world, n), dtype=dtype, device=device)
+            self.seqbuf = torch.full((nslot, self.world), -1, dtype=torch.int64, device=device)
+
+    def push(self, src, seq):
+        slot = seq % self.nslot
+        if self.rank == self.root:
+            self.dist.gather(src.reshape(-1), list(self.buf[slot].unbind(0)), dst=self.root)
+            self.seqbuf[slot].fill_(seq)
+        else:
+            self.dist.gather(src.reshape(-1), None, dst=self.root)
+
+    def finish(self):
+        self.dist.barrier()
+
+    def slot_on_root(self, seq):
+        if self.rank != self.root:
+            return None, None
+        return self.buf[seq % self.nslot], self.seqbuf[seq % self.nslot]
+
+
 def assemble_visibilities(parts):
     """Rank-ordered list of slab buffers int32 [2][nchan_slab][W] -> full band [2][nchan_total][W] (a view-level
     concatenation along channel; used by rank 0 after gather_to_root)."""

@@ -53,6 +53,18 @@ def _worker(rank, world, port, q):
                 assert np.array_equal(full, pl * 10000 + ch * 100 + wd + dump)
             else:
                 assert parts is None
+        # the per-step exchange (fast dump / beam powers pushed to rank 0 every step, two slots)
+        gs = sharding.GatherStream(5, torch.int32, "cpu", dist, nslot=2, root=0)
+        for step in range(5):
+            gs.push(torch.full((5,), 100 * step + rank, dtype=torch.int32), step)
+            if rank == 0:
+                payload, seqs = gs.slot_on_root(step)
+                assert seqs.tolist() == [step] * world
+                assert [int(payload[r][0]) for r in range(world)] == [100 * step + r for r in range(world)]
+                if step >= 1:                                    # the other slot still holds the previous step
+                    prev, pseq = gs.slot_on_root(step - 1)
+                    assert pseq.tolist() == [step - 1] * world and int(prev[world - 1][4]) == 100 * (step - 1) + world - 1
+        gs.finish()
         # max-over-ranks timing reduction as bench.py does it
         t = torch.tensor([float(rank + 1)], dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
