@@ -13,13 +13,27 @@ Differences that do not change the data products:
   * ``test=True`` cross-checks every dump on the GPU against the independent CUDA-core kernel instead of running
     numpy for ~10 minutes per gulp (corr_block.py:265-315).
 
-Optional fused fast-dump path (BASELINE configs[4]): three extra keyword arguments at the END of the signature,
-``fast_oring=None, nchan_sum=4, fast_nvis=4704``.  With ``fast_oring`` set, every integration is also written to that
-ring as CorrSubsel would write it (int32 [nchan/nchan_sum][nvis][2], CorrSubsel's header keys,
+Optional keyword arguments at the END of the signature (all default to the reference's behaviour):
+
+``fast_oring=None, nchan_sum=4, fast_nvis=4704`` -- fused fast dump (BASELINE configs[4]).  Every integration is also
+written to ``fast_oring`` as CorrSubsel would write it (int32 [nchan/nchan_sum][nvis][2], CorrSubsel's header keys,
 corr_subsel_block.py:272-285) -- gathered inside the correlator kernel's epilogue (``xeng_corr_accumulate_subsel``), so
 no CorrSubsel block and no second pass over the 383 MB matrix are needed.  The selection is set with
 ``update_fast_subsel(baselines)`` (same [[stand0, pol0], [stand1, pol1]] lists as CorrSubsel's ``baselines`` key) and
-takes effect at the next integration boundary.
+takes effect at the next integration boundary.  The ring may live in any space: for anything but 'cuda' (production
+uses a 'cuda_host' ring, lwa352-pipeline.py:155) the kernel gathers into a device scratch buffer that is copied into
+the span when the integration closes -- the kernel's reductions never cross PCIe.
+
+``acc_oring=None, slow_acc_len=None`` -- fused CorrAcc.  With ``acc_oring`` set (and ``oring=None``), the long
+integration CorrAcc would form from this block's dumps (lwa352-pipeline.py:232-276: Corr -> CorrAcc) is accumulated
+by the SAME launch straight into a span of ``acc_oring``: ``slow_acc_len`` samples per dump (a multiple of
+``acc_len``), CorrAcc's header keys (``upstream_acc_len``, ``acc_len``, ``seq0``; corr_acc_block.py:216,255-256).
+``acc_len`` then only sets the fast dump's cadence.  One launch per gulp does: long accumulator read-modify-write +
+fast-dump gather -- the path bench.py's headline number times.
+
+``gulps_per_span=1`` -- read ``gulps_per_span`` gulps per input span and launch them back to back, waiting for the
+device once per span (and at integration ends) instead of once per gulp: the host bookkeeping of one gulp then
+overlaps the kernel of the previous one.
 """
 import contextlib
 import json
@@ -51,8 +65,15 @@ def regtile_index(in0, in1, nstand):
 class Corr(Block):
     def __init__(self, log, iring, oring, ntime_gulp=2500, guarantee=True, core=-1, nchan=192, npol=2, nstand=352,
                  acc_len=2400, gpu=-1, test=False, etcd_client=None, autostartat=0, ant_to_input=None,
-                 fast_oring=None, nchan_sum=4, fast_nvis=4704):
+                 fast_oring=None, nchan_sum=4, fast_nvis=4704, acc_oring=None, slow_acc_len=None, gulps_per_span=1):
         assert (acc_len % ntime_gulp == 0), "Acculmulation length must be a multiple of gulp size"
+        if acc_oring is not None:
+            if oring is not None:
+                raise ValueError("Corr: with acc_oring (fused CorrAcc) the per-integration matrix is not produced; pass oring=None")
+            if not slow_acc_len or slow_acc_len % acc_len:
+                raise ValueError("Corr: slow_acc_len must be a positive multiple of acc_len")
+        elif oring is None:
+            raise ValueError("Corr: need oring or acc_oring")
         super(Corr, self).__init__(log, iring, oring, guarantee, core, etcd_client=etcd_client)
         self.ntime_gulp, self.nchan, self.npol, self.nstand = ntime_gulp, nchan, npol, nstand
         self.matlen = nchan * (nstand // 2 + 1) * (nstand // 4) * npol * npol * 4
@@ -89,6 +110,11 @@ class Corr(Block):
         self.fast_gulp_size = (nchan // nchan_sum) * fast_nvis * 8
         self._fast_baselines = [[[i % nstand, 0], [i % nstand, 0]] for i in range(fast_nvis)]   # corr_subsel_block.py:230
         self._fast_pending = fast_oring is not None
+        self._fast_dev = None        # device scratch of the fast dump when fast_oring is not a 'cuda' ring
+        if fast_oring is not None and getattr(fast_oring, 'space', 'cuda') != 'cuda':
+            self._fast_dev = rt.zeros(self.fast_gulp_size // 4, 'i32', 'cuda')
+        self.acc_oring, self.slow_acc_len = acc_oring, slow_acc_len
+        self.gulps_per_span = max(1, int(gulps_per_span))
 
     def update_fast_subsel(self, baselines):
         """Selection of the fused fast dump: ``fast_nvis`` entries [[stand0, pol0], [stand1, pol1]]; loaded at the
@@ -149,17 +175,23 @@ class Corr(Block):
         return ok
 
     # ------------------------------------------------------------------ main loop
+    def _set_state(self, state):
+        if self.stats.get('state') != state:        # published on change only: a ProcLog update per gulp is pure overhead
+            self.update_stats({'state': state})
+
     def main(self):
         rt.set_core(self.core)
         rt.set_device(self.gpu)
         self.bind_proclog.update({'ncore': 1, 'core0': rt.get_core()})
-        self.oring.resize(self.ogulp_size)
+        fused_acc = self.acc_oring is not None
+        main_ring = self.acc_oring if fused_acc else self.oring
+        main_ring.resize(self.ogulp_size)
         step = self.ntime_gulp
         clock = IntegrationClock(recover_skip=10, asap="boundary")
         time_tag = 1
         self.update_stats({'state': 'starting'})
         with contextlib.ExitStack() as stack:
-            oring = stack.enter_context(self.oring.begin_writing())
+            oring = stack.enter_context(main_ring.begin_writing())
             foring = None
             if self.fast_oring is not None:
                 self.fast_oring.resize(self.fast_gulp_size)
@@ -168,6 +200,7 @@ class Corr(Block):
             self.update_pending = True          # load the constructor's start_time / acc_len on the first gulp
             oseq = ospan = None
             foseq = fspan = None
+            slow_first = slow_last = None       # fused CorrAcc: window of the long integration
             for iseq in self.iring.read(guarantee=self.guarantee):
                 self.log.info('CORR >> new input sequence!')
                 ihdr = json.loads(iseq.header.tostring())
@@ -183,53 +216,67 @@ class Corr(Block):
                 self.sequence_proclog.update(ohdr)
                 ospan = fspan = None            # an integration cut short by the end of a sequence is dropped
                 process_time = acquire_time = reserve_time = 0.
-                for ispan in iseq.read(self.igulp_size):
-                    if ispan.size < self.igulp_size:
+                for ispan in iseq.read(self.gulps_per_span * self.igulp_size):
+                    ngulp = ispan.size // self.igulp_size
+                    if ngulp == 0:
                         self.log.info("CORR >>> Ignoring final gulp (expected %d bytes but got %d)"
                                       % (self.igulp_size, ispan.size))
                         continue
-                    if self.update_pending:
-                        self.update_command_vals()
-                        clock.retarget(self.command_vals['start_time'], self.command_vals['acc_len'], now)
-                        self.log.info("CORR >> New start time set to %d. Accumulating %d samples"
-                                      % (clock.start_time, clock.acc_len))
-                        ohdr['acc_len'], ohdr['seq0'] = clock.acc_len, clock.start_time
-                    self.update_stats({'curr_sample': now})
-                    if clock.acc_len == 0:      # stop condition
-                        self.update_stats({'state': 'stopped'})
-                        if oseq:
-                            oseq.end()
-                        if foseq:
-                            foseq.end()
-                        oseq = ospan = foseq = fspan = None
-                        clock.stop()
-                        now += step
-                        continue
-                    if clock.begins(now, step):
-                        self.log.info("CORR >> Start time %d reached." % clock.start_time)
-                        if oseq:
-                            oseq.end()
-                        self.sequence_proclog.update(ohdr)
-                        oseq = oring.begin_sequence(time_tag=time_tag, header=json.dumps(ohdr),
-                                                    nringlet=iseq.nringlet)
-                        if foring is not None:
+                    in_flight = False           # launches of this span the device may still be running
+                    for k in range(ngulp):
+                        idata = ispan.data if ngulp == 1 and ispan.size == self.igulp_size else \
+                            ispan.data[k * self.igulp_size:(k + 1) * self.igulp_size]
+                        if self.update_pending:
+                            self.update_command_vals()
+                            clock.retarget(self.command_vals['start_time'], self.command_vals['acc_len'], now)
+                            self.log.info("CORR >> New start time set to %d. Accumulating %d samples"
+                                          % (clock.start_time, clock.acc_len))
+                            ohdr['acc_len'], ohdr['seq0'] = clock.acc_len, clock.start_time
+                            if fused_acc and clock.acc_len and self.slow_acc_len % clock.acc_len:
+                                self.log.error("CORR >> acc_len %d does not divide slow_acc_len %d"
+                                               % (clock.acc_len, self.slow_acc_len))
+                        self.stats['curr_sample'] = now         # published with the next update_stats
+                        if clock.acc_len == 0:      # stop condition
+                            self._set_state('stopped')
+                            if oseq:
+                                oseq.end()
                             if foseq:
                                 foseq.end()
-                            fhdr = self._fast_header(ohdr, self._load_fast_selection())
-                            foseq = foring.begin_sequence(time_tag=time_tag, header=json.dumps(fhdr),
-                                                          nringlet=iseq.nringlet)
-                        time_tag += 1
-                    if not clock.running:
-                        self.update_stats({'state': 'waiting'})
-                        now += step
-                        continue
-                    self.update_stats({'state': 'running'})
-                    t = time.time()
-                    acquire_time, prev = t - prev, t
-                    is_first, is_last = (now == clock.first), (now == clock.last)
-                    if is_first:
-                        ospan = rt.WriteSpan(oseq.ring, self.ogulp_size, nonblocking=False)
-                        if foring is not None:
+                            oseq = ospan = foseq = fspan = None
+                            clock.stop()
+                            now += step
+                            continue
+                        if clock.begins(now, step):
+                            self.log.info("CORR >> Start time %d reached." % clock.start_time)
+                            if oseq:
+                                oseq.end()
+                            mhdr = dict(ohdr)
+                            if fused_acc:           # CorrAcc's output header (corr_acc_block.py:216,255-256)
+                                mhdr.update({'upstream_acc_len': clock.acc_len, 'acc_len': self.slow_acc_len, 'seq0': now})
+                                slow_first, slow_last = now, now + self.slow_acc_len - step
+                                ospan = None
+                            self.sequence_proclog.update(mhdr)
+                            oseq = oring.begin_sequence(time_tag=time_tag, header=json.dumps(mhdr),
+                                                        nringlet=iseq.nringlet)
+                            if foring is not None:
+                                if foseq:
+                                    foseq.end()
+                                fhdr = self._fast_header(ohdr, self._load_fast_selection())
+                                foseq = foring.begin_sequence(time_tag=time_tag, header=json.dumps(fhdr),
+                                                              nringlet=iseq.nringlet)
+                            time_tag += 1
+                        if not clock.running:
+                            self._set_state('waiting')
+                            now += step
+                            continue
+                        self._set_state('running')
+                        t = time.time()
+                        acquire_time, prev = t - prev, t
+                        is_first, is_last = (now == clock.first), (now == clock.last)
+                        acc_first, acc_last = (now == slow_first, now == slow_last) if fused_acc else (is_first, is_last)
+                        if acc_first:
+                            ospan = rt.WriteSpan(oseq.ring, self.ogulp_size, nonblocking=False)
+                        if is_first and foring is not None:
                             if self._fast_pending:      # new selection: new fast sequence with an updated header
                                 foseq.end()
                                 fhdr = self._fast_header(ohdr, self._load_fast_selection())
@@ -238,38 +285,53 @@ class Corr(Block):
                                                               nringlet=iseq.nringlet)
                                 time_tag += 1
                             fspan = rt.WriteSpan(foseq.ring, self.fast_gulp_size, nonblocking=False)
-                        t = time.time()
-                        reserve_time, prev = t - prev, t
-                    if ospan is None:
-                        self.log.error("CORR: trying to write to not-yet-opened ospan")
-                        now += step
-                        continue
-                    # device boundary (replaces _bf.bfXgpuKernel, corr_block.py:445): ospan (+)= X(ispan)
-                    if fspan is not None:       # the same launch also gathers the fast-dump selection
-                        self._xcorr.accumulate_subsel(ispan.data, ospan.data, is_first, fspan.data, is_first)
-                    else:
-                        self._xcorr.accumulate(ispan.data, ospan.data, is_first)
-                    if self.test:
-                        self._crosscheck_gulp(ispan.data, is_first)
-                    self._xcorr.sync()          # the input span may be released when this iteration ends
-                    t = time.time()
-                    process_time += t - prev
-                    prev = t
-                    if is_last:
+                        if acc_first or is_first:
+                            t = time.time()
+                            reserve_time, prev = t - prev, t
+                        if ospan is None:
+                            self.log.error("CORR: trying to write to not-yet-opened ospan")
+                            now += step
+                            continue
+                        # device boundary (replaces _bf.bfXgpuKernel, corr_block.py:445): ospan (+)= X(ispan)
+                        if fspan is not None:       # the same launch also gathers the fast-dump selection
+                            ftarget = self._fast_dev if self._fast_dev is not None else fspan.data
+                            self._xcorr.accumulate_subsel(idata, ospan.data, acc_first, ftarget, is_first)
+                        else:
+                            self._xcorr.accumulate(idata, ospan.data, acc_first)
                         if self.test:
-                            self._crosscheck_compare(ospan.data)
-                        ospan.close()
-                        ospan = None
-                        if fspan is not None:
-                            fspan.close()
-                            fspan = None
-                        gbps = 8 * clock.acc_len * ihdr['nchan'] * ihdr['nstand'] * ihdr['npol'] / process_time / 1e9
-                        self.perf_proclog.update({'acquire_time': acquire_time, 'reserve_time': reserve_time,
-                                                  'process_time': process_time, 'gbps': gbps})
-                        self.update_stats({'last_end_sample': now, 'throughput': gbps})
-                        process_time = 0.
-                        clock.advance(step)
-                    now += step
+                            self._crosscheck_gulp(idata, acc_first)
+                        in_flight = True
+                        if is_last or acc_last:
+                            if is_last and fspan is not None and self._fast_dev is not None:
+                                rt.copy_array(fspan.data, self._fast_dev)    # queued behind the kernel, then the sync
+                            self._xcorr.sync()      # spans are committed only once the device has written them
+                            in_flight = False
+                            t = time.time()
+                            process_time += t - prev
+                            prev = t
+                        if acc_last:
+                            if self.test:
+                                self._crosscheck_compare(ospan.data)
+                            ospan.close()
+                            ospan = None
+                            if fused_acc:
+                                slow_first, slow_last = slow_last + step, slow_last + self.slow_acc_len
+                        if is_last:
+                            if fspan is not None:
+                                fspan.close()
+                                fspan = None
+                            gbps = 8 * clock.acc_len * ihdr['nchan'] * ihdr['nstand'] * ihdr['npol'] / max(process_time, 1e-9) / 1e9
+                            self.perf_proclog.update({'acquire_time': acquire_time, 'reserve_time': reserve_time,
+                                                      'process_time': process_time, 'gbps': gbps})
+                            self.update_stats({'last_end_sample': now, 'throughput': gbps})
+                            process_time = 0.
+                            clock.advance(step)
+                        now += step
+                    if in_flight:
+                        self._xcorr.sync()          # the input span is released when this iteration ends
+                        t = time.time()
+                        process_time += t - prev
+                        prev = t
                 if oseq:
                     oseq.end()
                 if foseq:
