@@ -149,6 +149,9 @@ class Beamform(Block):
                         if copy_pending:
                             self.log.debug("BEAMFORM >> Copy coefficients to GPU at time %d" % now)
                             rt.copy_array(self.gains_gpu, self.gains_cpu)
+                            # the tensor-core kernel reads the weights as int8 digit planes: converted here, once per
+                            # update, instead of with every gulp (bfBeamformRun takes them per call, :449)
+                            self._bf.set_weights(self.gains_gpu)
                             copy_pending = False
                         t = time.time()
                         acquire_time, prev = t - prev, t
@@ -156,9 +159,9 @@ class Beamform(Block):
                             t = time.time()
                             reserve_time, prev = t - prev, t
                             if self.ntime_sum is None:
-                                self._bf.run(ispan.data, ospan.data, self.gains_gpu)
+                                self._bf.run(ispan.data, ospan.data, None)
                             else:
-                                self._bf.run_integrate(ispan.data, ospan.data, self.gains_gpu, self.ntime_sum)
+                                self._bf.run_integrate(ispan.data, ospan.data, None, self.ntime_sum)
                             self._bf.sync()
                         now += self.ntime_gulp
                         t = time.time()

@@ -206,6 +206,11 @@ class WriteSequence(object):
     def reserve(self, size, nonblocking=False):
         return WriteSpan(self.ring, size, nonblocking=nonblocking, _seq=self._seq)
 
+    def commit_buffer(self, buf, nbytes=None):
+        """Commit an existing buffer (already in the ring's space) as the next span, zero-copy: what a writer
+        achieves on a real ring by producing straight into the span it reserved."""
+        self.ring._commit(self._seq, buf, len(buf) if nbytes is None else int(nbytes))
+
     def end(self):
         with self.ring._cv:
             self._seq.ended = True

@@ -37,8 +37,24 @@ class FakeXCorr(object):
             out[1] += 1
         CALLS.append(("corr", tag, bool(first)))
 
+    def set_subsel(self, vismap, conj, nchan_sum=4):
+        self.sel0 = int(np.asarray(vismap).reshape(-1)[0]) if np.asarray(vismap).size else -1
+        CALLS.append(("set_subsel", self.sel0, int(nchan_sum)))
+
+    def accumulate_subsel(self, d_in, d_acc, first, d_sub_out, sub_first=True):
+        """accumulate() + the fast dump: sub.int32[0] (=|+=) tag, sub.int32[1] = first entry of the selection."""
+        self.accumulate(d_in, d_acc, first)
+        tag = int(_np(d_in)[0])
+        sub = _np(d_sub_out).view(np.int32)
+        if sub_first:
+            sub[0] = tag
+        else:
+            sub[0] += tag
+        sub[1] = getattr(self, "sel0", -1)
+        CALLS.append(("corr_sub", tag, bool(first), bool(sub_first)))
+
     def sync(self):
-        pass
+        CALLS.append(("corr_sync",))
 
     def close(self):
         pass
@@ -72,9 +88,13 @@ class FakeBeamformer(object):
     def __init__(self, gpu=-1, ninput=704, nchan=192, ntime=480, nbeam=16, ntime_blocks=0, stream=None):
         self.dims = (ninput, nchan, ntime, nbeam, ntime_blocks)
 
-    def run(self, d_in, d_out, d_w):
+    def set_weights(self, d_w):
+        self.w = _np(d_w).view(np.complex64).copy()      # a snapshot, as the digit-plane conversion is
+        CALLS.append(("bf_set_weights",))
+
+    def run(self, d_in, d_out, d_w=None):
         _np(d_out)[0] = _np(d_in)[0]
-        w = _np(d_w).view(np.complex64)
+        w = _np(d_w).view(np.complex64) if d_w is not None else self.w
         CALLS.append(("bf_run", int(_np(d_in)[0]), w.copy()))
 
     def run_integrate(self, d_in, d_out, d_w, ntime_sum):

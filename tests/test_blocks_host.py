@@ -209,6 +209,54 @@ def test_corr_realigns_on_new_sequence_and_stops_on_zero(host_only):
     assert drain(oring, c.ogulp_size) == [] and c.stats['state'] == 'stopped'
 
 
+def test_corr_fused_corracc_and_fast_dump_on_a_host_ring(host_only):
+    """Corr(oring=None, acc_oring=..., slow_acc_len=..., fast_oring=<cuda_host ring>): one launch per gulp feeds the
+    long accumulator (CorrAcc's span + header keys, corr_acc_block.py:216,255-256) and the fast dump (CorrSubsel's
+    header keys, corr_subsel_block.py:272-285); the fast dump of a non-device ring goes through the device scratch."""
+    iring, slow, fastr = ringshim.Ring("gpu-input"), ringshim.Ring("corr-slow-output"), ringshim.Ring("fast", space="cuda_host")
+    c = make_corr(iring, None, acc_len=2 * NT, autostartat=0, acc_oring=slow, slow_acc_len=4 * NT, fast_oring=fastr,
+                  nchan_sum=2, fast_nvis=6, ant_to_input=np.arange(NSTAND * NPOL).reshape(NSTAND, NPOL))
+    assert c._fast_dev is not None
+    g = c.igulp_size
+    fill(iring, [(base_header(0), [gulp(t, g) for t in range(1, 11)])])
+    c.main()
+    (hdr, spans), = drain(slow, c.ogulp_size)
+    assert hdr['upstream_acc_len'] == 2 * NT and hdr['acc_len'] == 4 * NT and hdr['seq0'] == 0
+    assert [tuple(s.view(np.int32)[:2]) for s in spans] == [(1 + 2 + 3 + 4, 4), (5 + 6 + 7 + 8, 4)]   # 9, 10: unfinished
+    (fhdr, fspans), = drain(fastr, c.fast_gulp_size)
+    assert fhdr['nvis'] == 6 and fhdr['nchan'] == NCHAN // 2 and fhdr['nchan_sum'] == 2 and fhdr['acc_len'] == 2 * NT
+    assert len(fhdr['baselines']) == 6
+    assert [int(s.view(np.int32)[0]) for s in fspans] == [1 + 2, 3 + 4, 5 + 6, 7 + 8, 9 + 10]
+    subs = [x for x in host_only.CALLS if x[0] == "corr_sub"]
+    assert [x[2] for x in subs] == [True, False, False, False, True, False, False, False, True, False]    # slow first
+    assert [x[3] for x in subs] == [True, False] * 5                                                      # fast first
+    with pytest.raises(ValueError):
+        make_corr(iring, ringshim.Ring(), acc_oring=slow, slow_acc_len=4 * NT)       # both outputs: not one launch
+    with pytest.raises(ValueError):
+        make_corr(iring, None, acc_len=2 * NT, acc_oring=slow, slow_acc_len=3 * NT)   # not a multiple of acc_len
+
+
+def test_corr_multi_gulp_spans_sync_once_per_span(host_only):
+    """gulps_per_span = 3: same dumps as one gulp per span, the device is waited for at integration ends and once per
+    input span -- not once per gulp; a short final span still yields its whole gulps."""
+    outs = []
+    for gps in (1, 3):
+        del host_only.CALLS[:]
+        iring, oring = ringshim.Ring(), ringshim.Ring()
+        c = make_corr(iring, oring, acc_len=4 * NT, autostartat=0, gulps_per_span=gps)
+        g = c.igulp_size
+        fill(iring, [(base_header(0), [gulp(t, g) for t in range(1, 9)])])
+        c.main()
+        (hdr, spans), = drain(oring, c.ogulp_size)
+        outs.append(([tuple(s.view(np.int32)[:2]) for s in spans],
+                     [x[1:] for x in host_only.CALLS if x[0] == "corr"],
+                     len([x for x in host_only.CALLS if x[0] == "corr_sync"])))
+    assert outs[0][0] == outs[1][0] == [(1 + 2 + 3 + 4, 4), (5 + 6 + 7 + 8, 4)]
+    assert outs[0][1] == outs[1][1]
+    assert outs[0][2] == 8           # one wait per gulp
+    assert outs[1][2] == 4           # spans end after gulps 3, 6, 8; integrations after 4 and 8 (8 coincides)
+
+
 # ------------------------------------------------------------------------------------------- CorrAcc
 def corr_out_header(seq0, acc_len, **kw):
     h = base_header(seq0, acc_len=acc_len, **kw)
