@@ -41,9 +41,9 @@ def _one(torch, nchan, ntime, ngulp, gulps_per_span, with_beam, slow_gulps, fast
     bufs = [torch.randint(0, 256, (span_gulps * ntime * nchan * NINPUT,), dtype=torch.uint8, device=dev, generator=gen)
             for _ in range(3)]
     iring = ringshim.Ring("gpu-input", space="cuda", maxspans=4)
-    slow = ringshim.Ring("corr-slow-output", space="cuda")
-    fast = ringshim.Ring("corr-fast-output", space=fast_space)
-    bfo = ringshim.Ring("bf-pow-output", space="cuda")
+    slow = ringshim.Ring("corr-slow-output", space="cuda", recycle=True)
+    fast = ringshim.Ring("corr-fast-output", space=fast_space, recycle=True)
+    bfo = ringshim.Ring("bf-pow-output", space="cuda", recycle=True)
     corr = Corr(log, iring, None, ntime_gulp=ntime, nchan=nchan, nstand=NSTAND, npol=NPOL, acc_len=ntime, autostartat=0,
                 ant_to_input=np.arange(NINPUT).reshape(NSTAND, NPOL), fast_oring=fast, acc_oring=slow,
                 slow_acc_len=slow_gulps * ntime, gulps_per_span=gulps_per_span)

@@ -223,6 +223,7 @@ class Corr(Block):
                                       % (self.igulp_size, ispan.size))
                         continue
                     in_flight = False           # launches of this span the device may still be running
+                    closing, last_ends = [], []  # output spans to commit / integrations ended, once the device is done
                     for k in range(ngulp):
                         idata = ispan.data if ngulp == 1 and ispan.size == self.igulp_size else \
                             ispan.data[k * self.igulp_size:(k + 1) * self.igulp_size]
@@ -301,37 +302,43 @@ class Corr(Block):
                         if self.test:
                             self._crosscheck_gulp(idata, acc_first)
                         in_flight = True
-                        if is_last or acc_last:
-                            if is_last and fspan is not None and self._fast_dev is not None:
-                                rt.copy_array(fspan.data, self._fast_dev)    # queued behind the kernel, then the sync
-                            self._xcorr.sync()      # spans are committed only once the device has written them
-                            in_flight = False
-                            t = time.time()
-                            process_time += t - prev
-                            prev = t
+                        if is_last and fspan is not None and self._fast_dev is not None:
+                            # non-device fast ring: the kernel gathered into device scratch; the copy into the span is
+                            # queued behind it (and ahead of the next gulp's launch, which zeroes the scratch again)
+                            rt.copy_array(fspan.data, self._fast_dev)
                         if acc_last:
-                            if self.test:
-                                self._crosscheck_compare(ospan.data)
-                            ospan.close()
+                            closing.append((ospan, True))
                             ospan = None
                             if fused_acc:
                                 slow_first, slow_last = slow_last + step, slow_last + self.slow_acc_len
                         if is_last:
                             if fspan is not None:
-                                fspan.close()
+                                closing.append((fspan, False))
                                 fspan = None
-                            gbps = 8 * clock.acc_len * ihdr['nchan'] * ihdr['nstand'] * ihdr['npol'] / max(process_time, 1e-9) / 1e9
-                            self.perf_proclog.update({'acquire_time': acquire_time, 'reserve_time': reserve_time,
-                                                      'process_time': process_time, 'gbps': gbps})
-                            self.update_stats({'last_end_sample': now, 'throughput': gbps})
-                            process_time = 0.
+                            last_ends.append(now)
                             clock.advance(step)
                         now += step
+                    # ---- end of the input span: ONE wait for the device covers every launch of the span; the output
+                    # spans whose integrations ended inside it are committed afterwards, in order (a span is committed
+                    # only once the device has written it; the input span is released when this iteration ends)
                     if in_flight:
-                        self._xcorr.sync()          # the input span is released when this iteration ends
+                        self._xcorr.sync()
                         t = time.time()
                         process_time += t - prev
                         prev = t
+                    for sp, is_matrix in closing:
+                        if is_matrix and self.test:
+                            self._crosscheck_compare(sp.data)
+                        sp.close()
+                    del closing[:]
+                    if last_ends:
+                        nint = len(last_ends)
+                        gbps = 8 * nint * clock.acc_len * ihdr['nchan'] * ihdr['nstand'] * ihdr['npol'] / max(process_time, 1e-9) / 1e9
+                        self.perf_proclog.update({'acquire_time': acquire_time, 'reserve_time': reserve_time,
+                                                  'process_time': process_time / nint, 'gbps': gbps})
+                        self.update_stats({'last_end_sample': last_ends[-1], 'throughput': gbps})
+                        process_time = 0.
+                        del last_ends[:]
                 if oseq:
                     oseq.end()
                 if foseq:

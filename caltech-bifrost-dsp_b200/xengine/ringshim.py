@@ -63,10 +63,8 @@ def alloc_bytes(nbytes, space):
         return torch.empty(nbytes, dtype=torch.uint8, device="cuda")
     if space == "cuda_host":
         if torch is not None:
-            t = torch.empty(nbytes, dtype=torch.uint8)
-            if torch.cuda.is_available():
-                t = t.pin_memory()
-            return t
+            # torch's caching host allocator: a block is reused once its previous owner has been dropped
+            return torch.empty(nbytes, dtype=torch.uint8, pin_memory=torch.cuda.is_available())
         return np.empty(nbytes, dtype=np.uint8)
     if space == "system":
         return np.empty(nbytes, dtype=np.uint8)
@@ -113,9 +111,13 @@ class _Sequence(object):
 
 
 class Ring(object):
-    def __init__(self, name="ring", space="system", maxspans=8):
+    def __init__(self, name="ring", space="system", maxspans=8, recycle=False):
         self.name = name
         self.space = space
+        # recycle: drop a span's memory once every guaranteed reader has moved past it, as a real ring reuses its
+        # buffer (long runs; allocators can then hand the block out again).  Off by default: tests read rings after
+        # the writers have finished, without a guarantee.
+        self._recycle = recycle
         self._cv = threading.Condition()
         self._seqs = []
         self._writing_done = False
@@ -272,7 +274,14 @@ class ReadSequence(object):
                 ichunk += 1
                 if self._rid in ring._consumed:
                     ring._consumed[self._rid] = serial + 1
+                    if ring._recycle and ichunk >= 2:       # the span BEFORE the one handed out now is released
+                        low = min(ring._consumed.values()) - 1
+                        for j in range(ichunk - 1):
+                            if seq.chunks[j][0] is not None and seq.chunks[j][2] < low:
+                                seq.chunks[j] = (None, 0, seq.chunks[j][2])
                 ring._cv.notify_all()
+                if buf is None:                             # recycled before this (late) reader got here
+                    continue
             if not pend and nbytes == gulp_size:      # the common case: zero-copy hand-over of a whole span
                 yield ReadSpan(buf[:nbytes] if len(buf) != nbytes else buf, nbytes)
                 continue

@@ -237,8 +237,9 @@ def test_corr_fused_corracc_and_fast_dump_on_a_host_ring(host_only):
 
 
 def test_corr_multi_gulp_spans_sync_once_per_span(host_only):
-    """gulps_per_span = 3: same dumps as one gulp per span, the device is waited for at integration ends and once per
-    input span -- not once per gulp; a short final span still yields its whole gulps."""
+    """gulps_per_span = 3: same dumps as one gulp per span, the device is waited for once per input span -- not once
+    per gulp -- and the output spans of integrations that ended inside the span are committed after that wait; a short
+    final span still yields its whole gulps."""
     outs = []
     for gps in (1, 3):
         del host_only.CALLS[:]
@@ -254,7 +255,7 @@ def test_corr_multi_gulp_spans_sync_once_per_span(host_only):
     assert outs[0][0] == outs[1][0] == [(1 + 2 + 3 + 4, 4), (5 + 6 + 7 + 8, 4)]
     assert outs[0][1] == outs[1][1]
     assert outs[0][2] == 8           # one wait per gulp
-    assert outs[1][2] == 4           # spans end after gulps 3, 6, 8; integrations after 4 and 8 (8 coincides)
+    assert outs[1][2] == 3           # input spans end after gulps 3, 6 and 8
 
 
 # ------------------------------------------------------------------------------------------- CorrAcc

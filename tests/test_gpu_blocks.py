@@ -185,6 +185,49 @@ def test_correlator_graph_fused_fast_dump(torch_cuda):
         assert np.array_equal(sp.view(np.int32).reshape(want.shape), want.astype(np.int32)), "slow dump %d" % k
 
 
+@pytest.mark.parametrize("gulps_per_span,fast_space", [(1, "cuda_host"), (3, "cuda_host"), (2, "cuda")])
+def test_correlator_graph_single_launch_long_accumulation_and_fast_dump(torch_cuda, gulps_per_span, fast_space):
+    """The headline path at block level: Corr(oring=None, acc_oring, slow_acc_len, fast_oring) -- ONE launch per gulp
+    does CorrAcc's long accumulation and CorrSubsel's fast dump (lwa352-pipeline.py:232-276: Corr -> CorrAcc +
+    CorrSubsel, same header keys on both output rings).  Fast ring in production's 'cuda_host' space (the kernel
+    gathers into device scratch), several gulps per input span, 4704 baselines, against the oracle."""
+    from xengine import ringshim
+    from xengine.blocks import Corr
+    nstand, npol, nchan, nt, nvis = 32, 2, 8, 32, 4704
+    fast_len, slow_len, ngulp = nt, 4 * nt, 14
+    rng = np.random.default_rng(0xabcd + gulps_per_span)
+    v = rng.integers(0, 256, size=(ngulp, nt, nchan, nstand, npol), dtype=np.uint8)
+    r_in = ringshim.Ring("gpu-input", space="cuda")
+    r_slow = ringshim.Ring("corr-slow-output", space="cuda_host")
+    r_fast = ringshim.Ring("corr-fast-output", space=fast_space)
+    hdr = header(nchan, nstand, npol)
+    corr = Corr(LOG, r_in, None, ntime_gulp=nt, nchan=nchan, npol=npol, nstand=nstand, acc_len=fast_len, gpu=0,
+                autostartat=nt, ant_to_input=np.array(hdr['ant_to_input']), fast_oring=r_fast, nchan_sum=4,
+                fast_nvis=nvis, acc_oring=r_slow, slow_acc_len=slow_len, gulps_per_span=gulps_per_span)
+    bls = [[[int(a), int(b)], [int(c), int(d)]] for a, b, c, d in
+           zip(rng.integers(0, nstand, nvis), rng.integers(0, 2, nvis), rng.integers(0, nstand, nvis),
+               rng.integers(0, 2, nvis))]
+    corr.update_fast_subsel(bls)
+    slow, fast = [], []
+    run_all([source(r_in, hdr, list(v)), threading.Thread(target=corr.main, name="Corr"),
+             sink(r_slow, corr.ogulp_size, slow), sink(r_fast, corr.fast_gulp_size, fast)])
+    x = [orc.corr_xgpu(v[g]) for g in range(ngulp)]
+    vm, cj = orc.baselines_to_vismap(bls, corr.antpol_to_bl, corr.bl_is_conj)
+    (fh, fspans), = fast
+    assert fh['nvis'] == nvis and fh['nchan'] == nchan // 4 and fh['acc_len'] == fast_len and fh['seq0'] == nt
+    assert len(fspans) == ngulp - 1                       # every gulp from the start time on
+    for k, sp in enumerate(fspans):
+        got = sp.view(np.int32).reshape(nchan // 4, nvis, 2)
+        assert np.array_equal(got, orc.subselect(x[1 + k], vm, cj, 4)), "fast dump %d" % k
+    (sh, sspans), = slow
+    assert sh['upstream_acc_len'] == fast_len and sh['acc_len'] == slow_len and sh['seq0'] == nt
+    assert 'ant_to_input' not in sh
+    assert len(sspans) == 3                               # gulps 1-4, 5-8, 9-12; 13 is an unfinished integration
+    for k, sp in enumerate(sspans):
+        want = sum(x[1 + 4 * k + j].astype(np.int64) for j in range(4))
+        assert np.array_equal(sp.view(np.int32).reshape(want.shape), want.astype(np.int32)), "slow dump %d" % k
+
+
 @pytest.mark.parametrize("use_cor_fmt", [True, False])
 def test_corr_output_full_packets(torch_cuda, use_cor_fmt):
     """gpu-input -> Corr -> CorrAcc -> (cuda_host ring) -> CorrOutputFull: every packet's payload equals the oracle's
