@@ -11,3 +11,5 @@ from .beamform_sum_block import BeamformSum  # noqa: F401
 from .beamform_sum_single_beam_block import BeamformSumSingleBeam  # noqa: F401
 from .beamform_output_block import BeamformOutput  # noqa: F401
 from .beamform_vlbi_output_block import BeamformVlbiOutput  # noqa: F401
+from .copy_block import Copy  # noqa: F401
+from .dummy_source_block import DummySource  # noqa: F401

@@ -121,3 +121,31 @@ def copy_array(dst, src):
         src = src.detach().cpu().numpy()
     np.copyto(dst.reshape(-1).view(np.uint8), np.ascontiguousarray(src).reshape(-1).view(np.uint8))
     return dst
+
+
+# ---------------------------------------------------------------------------------------------- streams / events
+class CopyLane(object):
+    """A private stream for copies plus an event per copy: ``copy(dst, src)`` enqueues and returns a ticket,
+    ``wait(ticket)`` blocks the calling thread until THAT copy has landed (work queued behind it keeps running).
+    On a machine without a CUDA device (host-only tests, 'system' rings) copies run synchronously."""
+
+    def __init__(self):
+        self.cuda = torch is not None and torch.cuda.is_available()
+        self.stream = torch.cuda.Stream() if self.cuda else None
+
+    def copy(self, dst, src):
+        if not self.cuda or not (isinstance(dst, torch.Tensor) and isinstance(src, torch.Tensor)):
+            copy_array(dst, src)
+            if self.cuda:
+                torch.cuda.current_stream().synchronize()
+            return None
+        with torch.cuda.stream(self.stream):
+            dst.view(-1).view(torch.uint8).copy_(src.reshape(-1).view(torch.uint8), non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+        return ev
+
+    @staticmethod
+    def wait(ticket):
+        if ticket is not None:
+            ticket.synchronize()

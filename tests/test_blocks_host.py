@@ -258,6 +258,46 @@ def test_corr_multi_gulp_spans_sync_once_per_span(host_only):
     assert outs[1][2] == 3           # input spans end after gulps 3, 6 and 8
 
 
+# ------------------------------------------------------------------------------------------- DummySource / Copy
+def test_dummy_source_header_ramp_and_copy_block(host_only, tmp_path):
+    """DummySource -> Copy -> ring: the reference's fixture (dummy_source_block.py:194-195 ramp byte = stand % 8,
+    :231-245 header) moved gulp by gulp by the Copy block (copy_block.py:92-160): headers unchanged, bytes
+    unchanged, a partial final gulp ignored, buffer_multiplier gulps per input span."""
+    from xengine.blocks import Copy, DummySource
+    r0, r1 = ringshim.Ring("capture", space="system"), ringshim.Ring("gpu-input", space="system")
+    src = DummySource(LOG, r0, ntime_gulp=NT, nchan=NCHAN, nstand=NSTAND, npol=NPOL, target_throughput=0,
+                      pipeline_id=3, header={'extra': 1}, ngulp=5)
+    assert src.gulp_size == NT * NCHAN * NSTAND * NPOL
+    assert src.get_test_data()[0, 0, 5, 1] == 0 + 5j                  # byte 5 = re 0, im 5
+    src.main()
+    cp = Copy(LOG, r0, r1, ntime_gulp=NT, nbyte_per_time=NCHAN * NSTAND * NPOL, buffer_multiplier=2)
+    assert cp.buf_size == 4 * 2 * src.gulp_size
+    cp.main()
+    (hdr, spans), = drain(r1, src.gulp_size)
+    assert hdr['nchan'] == NCHAN and hdr['system_nchan'] == 32 * NCHAN and hdr['fs_hz'] == 196608000
+    assert hdr['bw_hz'] == 24e3 * NCHAN and hdr['seq0'] == 0 and hdr['pipeline_id'] == 3 and hdr['extra'] == 1
+    assert hdr['ant_to_input'] == np.arange(NSTAND * NPOL).reshape(NSTAND, NPOL).tolist()
+    assert hdr['input_to_ant'][5] == [2, 1]
+    assert len(spans) == 5
+    want = np.broadcast_to((np.arange(NSTAND, dtype=np.uint8) % 8)[None, None, :, None], (NT, NCHAN, NSTAND, NPOL))
+    for sp in spans:
+        assert np.array_equal(sp.reshape(NT, NCHAN, NSTAND, NPOL), want)
+    # test file source: gulps taken round-robin from the file; a short last input span is dropped by Copy
+    raw = np.random.default_rng(0).integers(0, 256, size=2 * src.gulp_size, dtype=np.uint8)
+    f = tmp_path / "vec.bin"
+    raw.tofile(str(f))
+    r0, r1 = ringshim.Ring(space="system"), ringshim.Ring(space="system")
+    DummySource(LOG, r0, ntime_gulp=NT, nchan=NCHAN, nstand=NSTAND, npol=NPOL, target_throughput=0, testfile=str(f),
+                ngulp=3).main()
+    (_, got), = drain(r0, src.gulp_size)
+    assert [bytes(g) for g in got] == [raw[:src.gulp_size].tobytes(), raw[src.gulp_size:].tobytes(), raw[:src.gulp_size].tobytes()]
+    r2 = ringshim.Ring(space="system")
+    fill(r2, [(base_header(0), [raw[:src.gulp_size], raw[:src.gulp_size // 2]])])
+    Copy(LOG, r2, r1, ntime_gulp=NT, nbyte_per_time=NCHAN * NSTAND * NPOL).main()
+    (_, got), = drain(r1, src.gulp_size)
+    assert len(got) == 1 and bytes(got[0]) == raw[:src.gulp_size].tobytes()
+
+
 # ------------------------------------------------------------------------------------------- CorrAcc
 def corr_out_header(seq0, acc_len, **kw):
     h = base_header(seq0, acc_len=acc_len, **kw)

@@ -228,6 +228,38 @@ def test_correlator_graph_single_launch_long_accumulation_and_fast_dump(torch_cu
         assert np.array_equal(sp.view(np.int32).reshape(want.shape), want.astype(np.int32)), "slow dump %d" % k
 
 
+def test_ingest_source_copy_corr_chain(torch_cuda):
+    """SURVEY 8 f2 as blocks: DummySource (pinned host ring, the reference's ramp fixture) -> Copy (H2D, one async copy
+    per gulp, committed as each lands) -> gpu-input ring -> Corr; and the on-device source (device ring) -> Corr.
+    Both dumps equal the oracle on the ramp (dummy_source_block.py:194-195: byte = stand % 8)."""
+    from xengine import ringshim
+    from xengine.blocks import Copy, Corr, DummySource
+    nstand, npol, nchan, nt, ngulp = 32, 2, 8, 32, 6
+    want = None
+    for on_device in (False, True):
+        r_host = ringshim.Ring("capture", space="cuda_host")
+        r_in = ringshim.Ring("gpu-input", space="cuda")
+        r_corr = ringshim.Ring("corr-output", space="cuda_host" if on_device else "cuda")
+        src = DummySource(LOG, r_in if on_device else r_host, ntime_gulp=nt, nchan=nchan, nstand=nstand, npol=npol,
+                          target_throughput=0, ngulp=ngulp)
+        corr = Corr(LOG, r_in, r_corr, ntime_gulp=nt, nchan=nchan, npol=npol, nstand=nstand, acc_len=3 * nt, gpu=0,
+                    autostartat=0, ant_to_input=src.ant_to_input)
+        out = []
+        threads = [threading.Thread(target=src.main, name="DummySource"), threading.Thread(target=corr.main, name="Corr"),
+                   sink(r_corr, corr.ogulp_size, out)]
+        if not on_device:
+            threads.append(threading.Thread(
+                target=Copy(LOG, r_host, r_in, ntime_gulp=nt, nbyte_per_time=nchan * nstand * npol, gpu=0,
+                            buffer_multiplier=2).main, name="Copy"))
+        run_all(threads)
+        (hdr, spans), = out
+        assert hdr['nchan'] == nchan and hdr['acc_len'] == 3 * nt and len(spans) == 2
+        if want is None:
+            want = 3 * orc.corr_xgpu(src.test_data).astype(np.int64)
+        for sp in spans:
+            assert np.array_equal(sp.view(np.int32).reshape(want.shape), want.astype(np.int32))
+
+
 @pytest.mark.parametrize("use_cor_fmt", [True, False])
 def test_corr_output_full_packets(torch_cuda, use_cor_fmt):
     """gpu-input -> Corr -> CorrAcc -> (cuda_host ring) -> CorrOutputFull: every packet's payload equals the oracle's
