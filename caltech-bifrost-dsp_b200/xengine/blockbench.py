@@ -51,7 +51,8 @@ def _one(torch, nchan, ntime, ngulp, gulps_per_span, with_beam, slow_gulps, fast
     bfo = ringshim.Ring("bf-pow-output", space="cuda", recycle=True)
     corr = Corr(log, iring, None, ntime_gulp=ntime, nchan=nchan, nstand=NSTAND, npol=NPOL, acc_len=ntime, autostartat=0,
                 ant_to_input=np.arange(NINPUT).reshape(NSTAND, NPOL), fast_oring=fast, acc_oring=slow,
-                slow_acc_len=slow_gulps * ntime, gulps_per_span=gulps_per_span)
+                slow_acc_len=slow_gulps * ntime,
+                gulps_per_span=1 if from_host else gulps_per_span)     # the Copy block commits gulp-sized spans
     prof = None
     if profile:
         import cProfile
