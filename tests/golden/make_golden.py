@@ -23,6 +23,8 @@ What is executed from the reference:
                                     -> golden_beamform.npz
   * pipeline/verification/tests/beamformer/beamformer_sum_test.py:
     SoftwareBfSum.cpu_sum_power     -> golden_beamsum.npz
+  * pipeline/test_transmitters/test_tx_vectors.py (whole script, its UDP socket replaced by a recorder)
+                                    -> golden_snap2_packets.npz
 
 Usage:  python tests/golden/make_golden.py
 """
@@ -225,5 +227,45 @@ def main():
     print("beamsum", ref_pow.shape)
 
 
+def snap2_packets():
+    """Run the reference's SNAP2 emulator (pipeline/test_transmitters/test_tx_vectors.py) unmodified on a small vector
+    file; its socket is replaced by a recorder that raises KeyboardInterrupt (which the script catches to stop) after
+    every spectrum of the file has been sent once."""
+    rng = np.random.RandomState(0x5a92)
+    ntime, nchan, nstand, npol = 6, 8, 64, 2
+    data = rng.randint(0, 256, [ntime, nchan, nstand, npol]).astype(np.uint8)
+    hdr = {"dtype": "np.uint8", "shape": list(data.shape), "ntime": ntime, "nchan": nchan, "nstand": nstand,
+           "npol": npol}
+    npkt = ntime * 2 * (nstand // 32)                      # -b 2 channel blocks x (nstand / 32) stand blocks
+    sent = []
+
+    class Recorder(object):
+        def __init__(self, *a, **k):
+            pass
+
+        def sendto(self, payload, addr):
+            if len(sent) >= npkt:
+                raise KeyboardInterrupt
+            sent.append(bytes(payload))
+
+    with tempfile.NamedTemporaryFile(suffix=".dat") as tf:
+        tf.write((json.dumps(hdr) + "\n").encode())
+        tf.write(data.tobytes())
+        tf.flush()
+        argv = ["test_tx_vectors.py", "-f", tf.name, "-b", "2"]
+        import socket as _socket
+        with mock.patch.object(sys, "argv", argv), mock.patch.object(_socket, "socket", Recorder):
+            runpy.run_path(os.path.join(REF, "pipeline/test_transmitters/test_tx_vectors.py"), run_name="__main__")
+    assert len(sent) == npkt and len(set(len(p) for p in sent)) == 1
+    np.savez_compressed(os.path.join(HERE, "golden_snap2_packets.npz"), data=data,
+                        packets=np.frombuffer(b"".join(sent), dtype=np.uint8).reshape(npkt, -1), nchan_blocks=2,
+                        nstand_per_pkt=32)
+    print("snap2", npkt, "packets of", len(sent[0]), "bytes")
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "snap2":
+        snap2_packets()
+    else:
+        main()
+        snap2_packets()

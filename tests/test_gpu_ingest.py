@@ -98,3 +98,24 @@ def test_packets_to_visibilities(torch_cuda):
     xc.accumulate(buf, acc, True)
     xc.sync()
     assert np.array_equal(acc.cpu().numpy(), orc.corr_xgpu(v.reshape(nt, nchan, nstand, 2)))
+
+
+def test_snap2_assemble_reference_transmitter_packets(torch_cuda, golden_dir):
+    """The packets the reference's own emulator sends (golden_snap2_packets.npz, recorded from
+    pipeline/test_transmitters/test_tx_vectors.py), shuffled, through xeng_snap2_assemble: the voltage buffer equals
+    the emulator's input vectors."""
+    import os
+    from xengine import ops
+    torch = torch_cuda
+    g = np.load(os.path.join(golden_dir, "golden_snap2_packets.npz"))
+    data, pkts = g["data"], g["packets"]
+    ntime, nchan, nstand, npol = data.shape
+    ninput = nstand * npol
+    order = np.random.default_rng(3).permutation(len(pkts))
+    raw = torch.from_numpy(np.ascontiguousarray(pkts[order])).cuda()
+    out = torch.full((ntime, nchan, ninput), 0xAA, dtype=torch.uint8, device="cuda")
+    nvalid = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ops.snap2_assemble(raw, len(pkts), pkts.shape[1], out, 0, ntime, nchan, ninput, 0, True, nvalid)
+    torch.cuda.synchronize()
+    assert int(nvalid) == len(pkts)
+    assert np.array_equal(out.cpu().numpy(), data.reshape(ntime, nchan, ninput))

@@ -203,3 +203,26 @@ def test_upchannelize_oracle_against_literal_dft():
         assert np.allclose(orc.upchan_beamform(v, w1 + 2 * w2), orc.upchan_beamform(v, w1) + 2 * orc.upchan_beamform(v, w2))
     w = orc.offline_beam_weights([50e6, 50.1e6], [0.0, 10.0, 4.0])
     assert w.shape == (2, 3) and np.allclose(w[:, 1], 1.0) and np.isclose(w[0, 0], np.exp(2j * np.pi * 50e6 * 10e-9))
+
+
+def test_snap2_oracle_against_the_reference_transmitter(golden_dir):
+    """Fixture produced by running the reference's own SNAP2 emulator, pipeline/test_transmitters/test_tx_vectors.py
+    (tests/golden/make_golden.py snap2_packets: its socket replaced by a recorder): every packet the reference sends
+    is byte-identical to orc.snap2_packet with the header fields of test_tx_vectors.py:100-106, and assembling the
+    recorded packets gives back the vector file the emulator was fed."""
+    g = np.load(os.path.join(golden_dir, "golden_snap2_packets.npz"))
+    data, pkts = g["data"], g["packets"]
+    ntime, nchan, nstand, npol = data.shape
+    ncb, spp = int(g["nchan_blocks"]), int(g["nstand_per_pkt"])
+    cpp = nchan // ncb
+    k = 0
+    for t in range(ntime):                      # emission order: seq, channel block, stand block
+        for cb in range(ncb):
+            for pb in range(nstand // spp):
+                payload = data[t, cb * cpp:(cb + 1) * cpp, pb * spp:(pb + 1) * spp, :].reshape(cpp, spp * npol)
+                want = orc.snap2_packet(t, 0, npol * spp, nstand * npol, cpp, nchan, cb, cb * cpp, pb * spp * npol, payload)
+                assert pkts[k].tobytes() == want, (t, cb, pb)
+                k += 1
+    assert k == len(pkts)
+    out, ngood = orc.snap2_assemble([p.tobytes() for p in pkts], 0, ntime, nchan, nstand * npol)
+    assert ngood == len(pkts) and np.array_equal(out, data.reshape(ntime, nchan, nstand * npol))
