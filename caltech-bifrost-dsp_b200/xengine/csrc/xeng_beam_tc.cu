@@ -278,85 +278,104 @@ __global__ void __launch_bounds__(BT_THREADS, 1) beamform_tc_kernel(BeamTcArgs a
 }
 
 // ----------------------------------------------------------------------------------------------------------------
-// fp32 weights -> digit planes.  One block per (channel, padded beam); thread tid owns inputs 16 tid .. 16 tid + 15.
+// fp32 weights -> digit planes.  One block per (channel, 4 beams): thread (chunk, bq) owns inputs 16 chunk .. +15 of beam
+// 4 quad + bq.  The four beams of a block are the eight rows (n & 7) of one core-matrix row group, and a thread
+// writes its beam's two adjacent rows (out_re, out_im) as 32 contiguous bytes, so four neighbouring lanes fill a whole
+// 128-byte core matrix: every store sector is complete.
 __device__ __forceinline__ void split_digits(int w, int (&d)[3]) {
   d[0] = static_cast<int8_t>(w & 0xFF);   // signed low byte
   w = (w - d[0]) / 256;                   // exact
   d[1] = static_cast<int8_t>(w & 0xFF);
   d[2] = (w - d[1]) / 256;                // in [-128, 127] for |W| <= 8 355 711
 }
+// x * 2^k for any int k, exact unless the result leaves the normal range (two clamped power-of-two factors)
+__device__ __forceinline__ float scale_pow2(float x, int k) {
+  const int k1 = max(-126, min(127, k)), k2 = max(-126, min(127, k - k1));
+  return x * __int_as_float((k1 + 127) << 23) * __int_as_float((k2 + 127) << 23);
+}
 
-__global__ void __launch_bounds__(128) beam_weight_digits_kernel(const float2* __restrict__ w, int8_t* __restrict__ dig,
-                                                                 float* __restrict__ scale, int nchan, int nbeam,
-                                                                 int ninput, int nb, int nbb, int nst) {
-  __shared__ float wmax[4];
-  const int c = blockIdx.x, bg = blockIdx.y, bb = bg / nb, bl = bg - bb * nb;
-  const int tid = threadIdx.x, i0 = 16 * tid;
-  const bool beam_ok = bg < nbeam;                         // padded beams of the last block: zero rows
-  float2 x[16];
+constexpr int WD_THREADS = 128;            // 32 chunks (512 inputs) x 4 beams per pass
+__global__ void __launch_bounds__(WD_THREADS) beam_weight_digits_kernel(const float2* __restrict__ w, int8_t* __restrict__ dig,
+                                                                        float* __restrict__ scale, int nchan, int nbeam,
+                                                                        int ninput, int nb, int nbb, int nst) {
+  __shared__ int smax[4];                  // per beam: max |component| as float bits (non-negative floats order as ints)
+  __shared__ int sbad;
+  const int c = blockIdx.x, quad = blockIdx.y;
+  const int tid = threadIdx.x, bq = tid & 3;
+  const int bg = quad * 4 + bq, bb = bg / nb, bl = bg - bb * nb;      // padded beam index, its block, index in block
+  const bool beam_ok = bg < nbeam;         // padded beams of the last block: zero rows
+  const float2* wrow = w + (static_cast<long>(c) * nbeam + bg) * ninput;
+  const int nchunk = nst * 4;
+  if (tid < 4) smax[tid] = 0;
+  if (tid == 0) sbad = 0;
+  __syncthreads();
+  // ---- pass 1: row maxima
   float mx = 0.f;
   bool bad = false;
+  for (int chunk = tid >> 2; chunk < nchunk; chunk += WD_THREADS / 4) {
+    const int i0 = 16 * chunk;
+    if (!beam_ok || i0 >= ninput) continue;
 #pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    x[k] = make_float2(0.f, 0.f);
-    if (beam_ok && i0 + k < ninput) x[k] = __ldg(w + (static_cast<long>(c) * nbeam + bg) * ninput + i0 + k);
-    const float ax = fabsf(x[k].x), ay = fabsf(x[k].y);
-    bad |= !(ax <= 3.0e38f) || !(ay <= 3.0e38f);           // inf / nan weights poison the whole row, as in fp32
-    mx = fmaxf(mx, fmaxf(ax, ay));
+    for (int k = 0; k < 16; k += 2) {      // ninput % 16 == 0: a chunk is all inside or all outside
+      const float4 v = __ldg(reinterpret_cast<const float4*>(wrow + i0 + k));
+      const float a0 = fabsf(v.x), a1 = fabsf(v.y), a2 = fabsf(v.z), a3 = fabsf(v.w);
+      bad |= !(a0 <= 3.0e38f) || !(a1 <= 3.0e38f) || !(a2 <= 3.0e38f) || !(a3 <= 3.0e38f);   // inf / nan
+      mx = fmaxf(mx, fmaxf(fmaxf(a0, a1), fmaxf(a2, a3)));
+    }
   }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-  const int anybad = __syncthreads_or(bad ? 1 : 0);
-  if ((tid & 31) == 0) wmax[tid >> 5] = mx;
+  atomicMax(&smax[bq], __float_as_int(mx));
+  if (bad) atomicOr(&sbad, 1 << bq);       // inf / nan weights poison their whole row, as they would in fp32
   __syncthreads();
-  mx = fmaxf(fmaxf(wmax[0], wmax[1]), fmaxf(wmax[2], wmax[3]));
+  mx = __int_as_float(smax[bq]);
+  const bool rowbad = (sbad >> bq) & 1;
   int e = 0;
   if (mx > 0.f) {
-    const float fr = frexpf(mx, &e);                       // mx = fr * 2^e, fr in [0.5, 1)
-    if (fr > 0.99607f) ++e;                                // keep |W| <= 127 * 65793 = 8 355 711 (three signed digits)
+    const float fr = frexpf(mx, &e);       // mx = fr * 2^e, fr in [0.5, 1)
+    if (fr > 0.99607f) ++e;                // keep |W| <= 127 * 65793 = 8 355 711 (three signed digits)
   }
-  if (tid == 0)
-    scale[(static_cast<long>(c) * nbb + bb) * BT_NB_MAX + bl] = anybad ? __int_as_float(0x7fc00000) : scalbnf(1.0f, e - 23);
-  if (tid >= nst * 4) return;
-
-  uint32_t pre[3][4], pim[3][4], pnim[3][4];               // 16 digit bytes each: w_re, w_im, -w_im
+  if (tid < 4)
+    scale[(static_cast<long>(c) * nbb + bb) * BT_NB_MAX + bl] = rowbad ? __int_as_float(0x7fc00000) : scale_pow2(1.0f, e - 23);
+  // ---- pass 2: quantise, split, store (the row is in L1 / L2 from pass 1)
+  const int N = 6 * nb;
+  const bool aligned = (reinterpret_cast<uintptr_t>(w) & 15) == 0;
+  for (int chunk = tid >> 2; chunk < nchunk; chunk += WD_THREADS / 4) {
+    const int i0 = 16 * chunk;
+    uint32_t pre[3][4], pim[3][4], pnim[3][4];               // 16 digit bytes each: w_re, w_im, -w_im
 #pragma unroll
-  for (int gdig = 0; gdig < 3; ++gdig)
+    for (int gdig = 0; gdig < 3; ++gdig)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) pre[gdig][j] = pim[gdig][j] = pnim[gdig][j] = 0u;
+      for (int j = 0; j < 4; ++j) pre[gdig][j] = pim[gdig][j] = pnim[gdig][j] = 0u;
+    if (beam_ok && i0 < ninput && !rowbad) {
 #pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    int wr = 0, wi = 0;
-    if (!anybad) {
-      wr = __float2int_rn(scalbnf(x[k].x, 23 - e));
-      wi = __float2int_rn(scalbnf(x[k].y, 23 - e));
+      for (int k = 0; k < 16; ++k) {
+        const float2 x = __ldg(wrow + i0 + k);
+        const int wr = __float2int_rn(scale_pow2(x.x, 23 - e)), wi = __float2int_rn(scale_pow2(x.y, 23 - e));
+        int dr[3], di[3], dn[3];
+        split_digits(wr, dr);
+        split_digits(wi, di);
+        split_digits(-wi, dn);
+#pragma unroll
+        for (int gdig = 0; gdig < 3; ++gdig) {
+          pre[gdig][k >> 2] |= static_cast<uint32_t>(dr[gdig] & 0xFF) << (8 * (k & 3));
+          pim[gdig][k >> 2] |= static_cast<uint32_t>(di[gdig] & 0xFF) << (8 * (k & 3));
+          pnim[gdig][k >> 2] |= static_cast<uint32_t>(dn[gdig] & 0xFF) << (8 * (k & 3));
+        }
+      }
     }
-    int dr[3], di[3], dn[3];
-    split_digits(wr, dr);
-    split_digits(wi, di);
-    split_digits(-wi, dn);
+    (void)aligned;
+    const int s = chunk >> 2, kq = chunk & 3;                // stage, 16-input chunk inside the stage
+    const int jre = kq >> 1, jim = 2 + (kq >> 1), k16 = kq & 1;
+    int8_t* stage = dig + ((static_cast<long>(c) * nbb + bb) * nst + s) * (static_cast<long>(N) * 2 * BT_KIN);
 #pragma unroll
     for (int gdig = 0; gdig < 3; ++gdig) {
-      pre[gdig][k >> 2] |= static_cast<uint32_t>(dr[gdig] & 0xFF) << (8 * (k & 3));
-      pim[gdig][k >> 2] |= static_cast<uint32_t>(di[gdig] & 0xFF) << (8 * (k & 3));
-      pnim[gdig][k >> 2] |= static_cast<uint32_t>(dn[gdig] & 0xFF) << (8 * (k & 3));
+      const int n_re = gdig * 2 * nb + 2 * bl;               // rows n_re (out_re) and n_re + 1 (out_im): 32 adjacent bytes
+      uint4* pj = reinterpret_cast<uint4*>(stage + jre * (N * 32) + (n_re >> 3) * 256 + k16 * 128 + (n_re & 7) * 16);
+      pj[0] = make_uint4(pre[gdig][0], pre[gdig][1], pre[gdig][2], pre[gdig][3]);        // out_re += v_re * w_re
+      pj[1] = make_uint4(pim[gdig][0], pim[gdig][1], pim[gdig][2], pim[gdig][3]);        // out_im += v_re * w_im
+      uint4* pi = reinterpret_cast<uint4*>(stage + jim * (N * 32) + (n_re >> 3) * 256 + k16 * 128 + (n_re & 7) * 16);
+      pi[0] = make_uint4(pnim[gdig][0], pnim[gdig][1], pnim[gdig][2], pnim[gdig][3]);    // out_re += v_im * (-w_im)
+      pi[1] = make_uint4(pre[gdig][0], pre[gdig][1], pre[gdig][2], pre[gdig][3]);        // out_im += v_im * w_re
     }
-  }
-  const int N = 6 * nb;
-  const int s = tid >> 2, kq = tid & 3;                    // stage, 16-input chunk inside the stage
-  const int jre = kq >> 1, jim = 2 + (kq >> 1), k16 = kq & 1;
-  int8_t* stage = dig + ((static_cast<long>(c) * nbb + bb) * nst + s) * (static_cast<long>(N) * 2 * BT_KIN);
-  auto put = [&](int j, int n, const uint32_t (&v)[4]) {
-    *reinterpret_cast<uint4*>(stage + j * (N * 32) + (n >> 3) * 256 + k16 * 128 + (n & 7) * 16) =
-        make_uint4(v[0], v[1], v[2], v[3]);
-  };
-#pragma unroll
-  for (int gdig = 0; gdig < 3; ++gdig) {
-    const int n_re = gdig * 2 * nb + 2 * bl, n_im = n_re + 1;
-    put(jre, n_re, pre[gdig]);      // out_re += v_re * w_re
-    put(jim, n_re, pnim[gdig]);     // out_re += v_im * (-w_im)
-    put(jre, n_im, pim[gdig]);      // out_im += v_re * w_im
-    put(jim, n_im, pre[gdig]);      // out_im += v_im * w_re
   }
 }
 
@@ -385,8 +404,9 @@ cudaError_t launch_beam_weight_digits(const float2* w, int8_t* dig, float* scale
                                       cudaStream_t stream) {
   BeamTcGeom g;
   if (!beam_tc_geometry(ninput, nchan, nbeam, &g)) return cudaErrorInvalidValue;
-  dim3 grid(nchan, g.nbb * g.nb);
-  beam_weight_digits_kernel<<<grid, 128, 0, stream>>>(w, dig, scale, nchan, nbeam, ninput, g.nb, g.nbb, g.nst);
+  if (reinterpret_cast<uintptr_t>(w) & 15) return cudaErrorInvalidValue;     // float4 loads of the weight rows
+  dim3 grid(nchan, g.nbb * g.nb / 4);
+  beam_weight_digits_kernel<<<grid, WD_THREADS, 0, stream>>>(w, dig, scale, nchan, nbeam, ninput, g.nb, g.nbb, g.nst);
   return cudaGetLastError();
 }
 
