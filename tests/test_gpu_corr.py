@@ -252,7 +252,10 @@ def test_subsel_and_reorder(torch_cuda):
 
 
 @pytest.mark.parametrize("shape,ncs,impl", [
-    ((96, 8, 64), 4, 0),     # TMA kernel, several tiles per channel
+    ((96, 8, 64), 4, 0),     # TMA kernel, grouped walk (channel sum inside a CTA), lists longer than 64 entries
+    ((96, 8, 64), 1, 0),     # nchan_sum = 1: every tile stores its own rows
+    ((64, 16, 100), 8, 0),   # groups of 8 channels, 10 tile positions
+    ((96, 32, 64), 16, 0),   # nchan_sum > 8: ungrouped walk, zeroing + reductions across CTAs
     ((130, 4, 68), 2, 0),    # ragged last row block, K not a multiple of the stage
     ((40, 8, 12), 4, 0),     # ninput = 24: not a multiple of 16 -> unfused fallback inside the library
     ((64, 4, 36), 1, 2),     # register-fed kernel -> unfused fallback
@@ -284,6 +287,15 @@ def test_corr_fused_accumulate_subsel(torch_cuda, shape, ncs, impl):
         xc.sync()
         assert np.array_equal(fast.cpu().numpy(), orc.subselect(x, vm, cj, ncs)), "fast dump of gulp %d" % g
         assert np.array_equal(acc.cpu().numpy(), want_acc.astype(np.int32)), "accumulator after gulp %d" % g
+    # sub_first = False: the fast dump integrates over several gulps (Corr's acc_len > ntime_gulp)
+    fast.fill_(-5)
+    want_fast = np.zeros((nchan // ncs, len(bls), 2), dtype=np.int64)
+    for g in range(3):
+        v = _voltages(rng, nt, nchan, nstand)
+        want_fast += orc.subselect(orc.corr_xgpu(v), vm, cj, ncs)
+        xc.accumulate_subsel(torch.from_numpy(v).cuda(), acc, False, fast, g == 0)
+    xc.sync()
+    assert np.array_equal(fast.cpu().numpy(), want_fast.astype(np.int32)), "fast dump integrated over 3 gulps"
     xc.set_subsel(np.zeros(0, np.int32), np.zeros(0, np.int32), ncs)     # cleared: the call must refuse
     with pytest.raises(Exception):
         xc.accumulate_subsel(torch.from_numpy(v).cuda(), acc, False, fast)
