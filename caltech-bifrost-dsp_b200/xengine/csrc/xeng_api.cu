@@ -163,11 +163,7 @@ int xeng_corr_set_impl(xeng_corr_t h, int impl) {
 }
 int64_t xeng_corr_matlen(xeng_corr_t h) { return h ? h->matlen : 0; }
 
-// fused fast dump: grouped tile walk (channel sum inside one CTA, no zeroing, no atomics) for the usual small nchan_sum
-static bool sub_grouped(xeng_corr_t h) { return h->sub_nsum >= 1 && h->sub_nsum <= 8; }
-
-static int corr_launch(xeng_corr_t h, const void* d_in, int32_t* d_out, int accumulate, int32_t* d_sub_out = nullptr,
-                       int sub_accumulate = 0) {
+static int corr_launch(xeng_corr_t h, const void* d_in, int32_t* d_out, int accumulate, int32_t* d_sub_out = nullptr) {
   xeng::CorrArgs a;
   a.in = static_cast<const uint8_t*>(d_in);
   a.out = d_out;
@@ -182,8 +178,6 @@ static int corr_launch(xeng_corr_t h, const void* d_in, int32_t* d_out, int accu
   a.trace = nullptr;
   a.sub_begin = h->d_sub_begin; a.sub_entries = h->d_sub_entries; a.sub_out = d_sub_out;
   a.sub_nvis = h->sub_nvis; a.sub_nsum = h->sub_nsum;
-  a.walk_group = (d_sub_out && sub_grouped(h)) ? h->sub_nsum : 1;
-  a.sub_accumulate = sub_accumulate;
   const char* trace_path = h->trace_path[0] ? h->trace_path : nullptr;   // developer-only: per-role timeline of CTA 0
   const size_t trace_bytes = 5 * 4096 * 2 * sizeof(long long);
   if (trace_path && a.ablate) {
@@ -321,9 +315,9 @@ int xeng_corr_accumulate_subsel(xeng_corr_t h, const void* d_in, void* d_acc, in
   if (h->sub_nvis <= 0) return fail(XENG_ERR_ARG, "no selection set: call xeng_corr_set_subsel first");
   int32_t* so = static_cast<int32_t*>(d_sub_out);
   if (corr_uses_tma(h, d_in, d_acc)) {   // one launch: correlate, accumulate in L2, sub-select from the staging buffers
-    if (sub_first && !sub_grouped(h))     // channel sums cross CTAs: zero first, the kernel adds
+    if (sub_first)
       XENG_CUDA(cudaMemsetAsync(so, 0, sizeof(int32_t) * 2 * h->sub_nvis * (h->nchan / h->sub_nsum), h->stream));
-    return corr_launch(h, d_in, static_cast<int32_t*>(d_acc), first ? 0 : 1, so, sub_first ? 0 : 1);
+    return corr_launch(h, d_in, static_cast<int32_t*>(d_acc), first ? 0 : 1, so);
   }
   // shapes the TMA kernel cannot take: per-gulp visibilities into a scratch buffer, then the stand-alone kernels
   const size_t words = static_cast<size_t>(2 * h->matlen);

@@ -95,32 +95,29 @@ struct Tile {
   int c, I, J;
 };
 struct TileWalk {
-  int g, cg, r, j;      // group index, its channel group and tile position, channel inside the group
+  int tile, c, r;
   __device__ __forceinline__ explicit TileWalk(const CorrArgs& a) {
-    g = blockIdx.x;
-    cg = 0;
+    tile = blockIdx.x;
+    c = 0;
     r = blockIdx.x;
-    j = 0;
     while (r >= a.tiles_per_chan) {
       r -= a.tiles_per_chan;
-      ++cg;
+      ++c;
     }
   }
-  __device__ __forceinline__ bool valid(const CorrArgs& a) const { return g < a.ngroups; }
+  __device__ __forceinline__ bool valid(const CorrArgs& a) const { return tile < a.ntiles; }
   __device__ __forceinline__ void next(const CorrArgs& a) {
-    if (++j < a.walk_group) return;
-    j = 0;
-    g += gridDim.x;
-    cg += a.step_c;
+    tile += gridDim.x;
+    c += a.step_c;
     r += a.step_r;
     if (r >= a.tiles_per_chan) {
       r -= a.tiles_per_chan;
-      ++cg;
+      ++c;
     }
   }
-  __device__ __forceinline__ Tile get(const CorrArgs& a) const {
+  __device__ __forceinline__ Tile get() const {
     Tile t;
-    t.c = cg * a.walk_group + j;
+    t.c = c;
     t.I = c_tile_I[r];
     t.J = c_tile_J[r];
     return t;
@@ -163,21 +160,11 @@ __device__ __forceinline__ uint4 parity_hi(uint4 a, uint4 b) {
   } while (0)
 
 constexpr uint32_t SUB_NONE = 0xFFFFFFFFu;
-// one selected word out of the staging buffer, imaginary part negated where the entry says conj
-__device__ __forceinline__ int sub_value(uint32_t stg_w, uint32_t en, int plane) {
+// one selected word: staging -> (negate the imaginary part where conj) -> out[v][plane] += value
+__device__ __forceinline__ void sub_emit(int32_t* so, uint32_t stg_w, uint32_t en, int plane) {
   int val = static_cast<int>(lds_u32(stg_w + (en & 0x3FFFu)));
   if (plane == 1 && ((en >> 14) & 1u)) val = -val;
-  return val;
-}
-__device__ __forceinline__ void sub_red(int32_t* so, uint32_t en, int val) {
   asm volatile("red.global.add.s32 [%0], %1;" ::"l"(so + static_cast<long>(en >> 15) * 2), "r"(val) : "memory");
-}
-__device__ __forceinline__ void sub_store(int32_t* so, uint32_t en, int val) {
-  asm volatile("st.global.s32 [%0], %1;" ::"l"(so + static_cast<long>(en >> 15) * 2), "r"(val) : "memory");
-}
-// ungrouped walk: out[v][plane] += value (the launcher zeroed the buffer)
-__device__ __forceinline__ void sub_emit(int32_t* so, uint32_t stg_w, uint32_t en, int plane) {
-  sub_red(so, en, sub_value(stg_w, en, plane));
 }
 
 template <bool ABL, bool SUB>
@@ -238,14 +225,9 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
     const uint32_t stg_w = smem_u32(staging) + warp * WARP_STAGING;
     const uint32_t my_run = stg_w + (b1 * 8 + A1l) * RUN_STRIDE + b1 * HALF_SKEW + p1 * 8;
     int it = 0;
-    // grouped fast dump: a lane's first two list entries are summed over the group's channels in registers
-    const bool sub_grouped = SUB && a.walk_group == a.sub_nsum;
-    int sa0_p0 = 0, sa0_p1 = 0, sa1_p0 = 0, sa1_p1 = 0;
-    (void)sa0_p0; (void)sa0_p1; (void)sa1_p0; (void)sa1_p1;
     for (TileWalk tw(a); tw.valid(a); tw.next(a), ++it) {
-      const Tile tl = tw.get(a);
+      const Tile tl = tw.get();
       const int buf = it & 1;
-      const bool g_first = tw.j == 0, g_last = tw.j == a.walk_group - 1;
       int sub_lb = 0, sub_le = 0;
       uint32_t sub_e0 = SUB_NONE, sub_e1 = SUB_NONE;
       if (SUB) {     // this (tile, warp)'s selection list; its global-load latency hides behind the accumulator wait
@@ -317,39 +299,12 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
         bulk_commit();
         if (SUB) {
           // fused CorrSubsel (corr_subsel_block.py:298): the selected words of this warp's 16 runs, straight from the
-          // staging buffer.  The first 64 entries of the list were fetched before the accumulator wait (sub_e0 / sub_e1).
+          // staging buffer; the nchan_sum channels of one output row come from different tiles -> red.global.add.
+          // The first 64 entries of the list were fetched before the accumulator wait (sub_e0 / sub_e1).
           int32_t* const so = a.sub_out + (static_cast<long>(tl.c / a.sub_nsum) * a.sub_nvis) * 2 + plane;
-          if (sub_grouped) {
-            // the nchan_sum channels of an output row are this CTA's consecutive tiles, and every one of them has
-            // the same list with the same lane assignment: sum in registers, ONE plain store at the group's end --
-            // no zeroing pass, no atomics.  Entries past the first 64 of a list: store on the first channel, then
-            // reductions by the same thread to the same address (program order).
-            const int v0 = sub_e0 != SUB_NONE ? sub_value(stg_w, sub_e0, plane) : 0;
-            const int v1 = sub_e1 != SUB_NONE ? sub_value(stg_w, sub_e1, plane) : 0;
-            int s0, s1;
-            if (plane == 0) {
-              s0 = sa0_p0 = g_first ? v0 : sa0_p0 + v0;
-              s1 = sa1_p0 = g_first ? v1 : sa1_p0 + v1;
-            } else {
-              s0 = sa0_p1 = g_first ? v0 : sa0_p1 + v0;
-              s1 = sa1_p1 = g_first ? v1 : sa1_p1 + v1;
-            }
-            if (g_last) {
-              if (sub_e0 != SUB_NONE) { if (a.sub_accumulate) sub_red(so, sub_e0, s0); else sub_store(so, sub_e0, s0); }
-              if (sub_e1 != SUB_NONE) { if (a.sub_accumulate) sub_red(so, sub_e1, s1); else sub_store(so, sub_e1, s1); }
-            }
-            for (int e = sub_lb + 64 + lane; e < sub_le; e += 32) {
-              const uint32_t en = a.sub_entries[e];
-              const int val = sub_value(stg_w, en, plane);
-              if (g_first && !a.sub_accumulate) sub_store(so, en, val);
-              else sub_red(so, en, val);
-            }
-          } else {
-            // channel sum across CTAs: out += value (buffer zeroed by the launcher)
-            if (sub_e0 != SUB_NONE) sub_emit(so, stg_w, sub_e0, plane);
-            if (sub_e1 != SUB_NONE) sub_emit(so, stg_w, sub_e1, plane);
-            for (int e = sub_lb + 64 + lane; e < sub_le; e += 32) sub_emit(so, stg_w, a.sub_entries[e], plane);
-          }
+          if (sub_e0 != SUB_NONE) sub_emit(so, stg_w, sub_e0, plane);
+          if (sub_e1 != SUB_NONE) sub_emit(so, stg_w, sub_e1, plane);
+          for (int e = sub_lb + 64 + lane; e < sub_le; e += 32) sub_emit(so, stg_w, a.sub_entries[e], plane);
         }
         XTRACE(4, 7);
       }
@@ -371,7 +326,7 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
     const uint32_t scratch = smem_u32(smem) + SCRATCH_OFF + (threadIdx.x - N_EPI_WARPS * 32) * 4;
     int gs0 = 0;                                                     // running stage index at the tile start
     for (TileWalk tw(a); tw.valid(a); tw.next(a), gs0 += n_kstage) {
-      const Tile tl = tw.get(a);
+      const Tile tl = tw.get();
       const uint32_t boff = (tl.I == tl.J) ? 0u : static_cast<uint32_t>(RAW_PANEL);   // diagonal: B raw == A raw
       for (int ks = (gs0 ^ grp) & 1; ks < n_kstage; ks += 2) {
         const int gs = gs0 + ks;
@@ -449,7 +404,7 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
     if (lane == 0 && !(ABL && (ablate & 64))) {
       int gs = 0;
       for (TileWalk tw(a); tw.valid(a); tw.next(a)) {
-        const Tile tl = tw.get(a);
+        const Tile tl = tw.get();
         const bool diag = (tl.I == tl.J);
         for (int ks = 0; ks < n_kstage; ++ks, ++gs) {
           const int rs = gs % RAW_STAGES;
@@ -559,9 +514,7 @@ cudaError_t launch_corr_swz(const CorrArgs& a_in, int nsm, cudaStream_t stream) 
     return e;
   }, kCfgCorrSwz);
   if (ce != cudaSuccess) return ce;
-  if (a.walk_group < 1 || a.nchan % a.walk_group) a.walk_group = 1;
-  a.ngroups = a.tiles_per_chan * (a.nchan / a.walk_group);
-  int grid = a.ngroups < nsm ? a.ngroups : nsm;
+  int grid = a.ntiles < nsm ? a.ntiles : nsm;
   if (grid <= 0) return cudaSuccess;
   a.step_c = grid / a.tiles_per_chan;
   a.step_r = grid % a.tiles_per_chan;

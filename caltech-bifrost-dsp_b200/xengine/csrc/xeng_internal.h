@@ -34,12 +34,6 @@ struct CorrArgs {
   int npairs;           // nstand / 2 (station pairs)
   int tiles_per_chan, ntiles;
   int step_c, step_r;   // grid / tiles_per_chan, grid % tiles_per_chan (filled by the TMA kernel's launcher)
-  // TMA kernel's tile walk: a CTA takes GROUPS of walk_group consecutive channels of one (I, J) tile position, one
-  // after the other (1: plain channel-major order).  With walk_group == sub_nsum the channel sum of the fused fast
-  // dump stays inside one CTA: registers + plain stores instead of zeroing + atomics.  ngroups = tiles_per_chan *
-  // nchan / walk_group.
-  int walk_group = 1, ngroups = 0;
-  int sub_accumulate = 0;   // fused fast dump: sub_out += selection (grouped walk; the ungrouped path always adds)
   int accumulate;       // 0: out = X, 1: out += X
   int ablate;           // profiling ablation mask (XENG_CORR_ABLATE, results invalid when != 0)
   long long* trace;     // developer timeline buffer (XENG_CORR_TRACE), null in production

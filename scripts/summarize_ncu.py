@@ -67,7 +67,7 @@ def full(src, dst):
         for r in data:
             f.write("== %s (ID %s)\n" % (r[name_col][:80], r[0]))
             for i, h in enumerate(hdr):
-                if h in KEYS:
+                if h in KEYS or "tensor" in h or "tmem" in h:    # every tensor-pipe / TMEM counter the report holds
                     f.write("  %-80s %s %s\n" % (h, r[i], units[i]))
     sys.stdout.write(open(dst).read())
     # steady-state (accumulating) launch = the one that also reads the accumulator: DRAM bytes per launch for bench.py
@@ -77,6 +77,7 @@ def full(src, dst):
         return float(r[i].replace(",", "")) * mult
     corr = [r for r in data if "corr_" in r[name_col]]
     if corr and len(sys.argv) > 4:
+        tag = sys.argv[5] if len(sys.argv) > 5 else ""
         r = max(corr, key=lambda r: num(r, "dram__bytes_read.sum"))
         out = {"dram_bytes_per_launch": num(r, "dram__bytes_read.sum") + num(r, "dram__bytes_write.sum"),
                "dram_bytes_read": num(r, "dram__bytes_read.sum"), "dram_bytes_write": num(r, "dram__bytes_write.sum"),
