@@ -285,15 +285,22 @@ def path_kernels(torch, ops, dev, nchan, hbm_peak, iters=10):
     res["corr_acc"] = {"ms": ms, "alg_bytes": 12 * nw, "gbs": 12 * nw / ms / 1e6, "frac_hbm": 12 * nw / ms / 1e6 / hbm_peak}
     a2i = np.arange(NINPUT, dtype=np.int32).reshape(NSTAND, NPOL)
     a2bl, conj = ops.get_order(a2i)
+    from oracle import xeng_oracle as orc_
+    real_vm, real_cj = real_selection(ops, orc_, np.random.default_rng(4704))
     for nvis in (4704, 4656):
-        sel = np.random.default_rng(nvis).integers(0, a2bl.size, nvis)
-        vm = torch.from_numpy(a2bl.reshape(-1)[sel].copy()).to(dev)
-        cj = torch.from_numpy(conj.reshape(-1)[sel].copy()).to(dev)
+        if nvis == 4704:      # CorrSubsel's shape: 48 stands, all pairs, 4 pol products each = whole 16-byte cells
+            vm, cj = torch.from_numpy(real_vm).to(dev), torch.from_numpy(real_cj).to(dev)
+        else:                 # the docs' count as random single words: every word in a cell of its own (worst case)
+            sel = np.random.default_rng(nvis).integers(0, a2bl.size, nvis)
+            vm = torch.from_numpy(a2bl.reshape(-1)[sel].copy()).to(dev)
+            cj = torch.from_numpy(conj.reshape(-1)[sel].copy()).to(dev)
         so = torch.zeros((nchan // 4, nvis, 2), dtype=torch.int32, device=dev)
         ms = timeit(lambda: ops.subsel(vis, so, vm, cj, nvis, nchan, 4, wpc))
         ab = 8 * nvis * nchan + 8 * nvis * nchan // 4
         res["corr_subsel_%d" % nvis] = {"ms": ms, "alg_bytes": ab, "gbs": ab / ms / 1e6,
-                                        "sector_bytes": 2 * 32 * nvis * nchan + 8 * nvis * nchan // 4}
+                                        "selection": "48 stands x all pairs x 4 pol products (whole cells)" if nvis == 4704
+                                        else "random single words",
+                                        "sector_bytes": 2 * 32 * (nvis // 4 if nvis == 4704 else nvis) * nchan + 8 * nvis * nchan // 4}
     ro = torch.zeros((NSTAND, NSTAND, 2, 2, nchan, 2), dtype=torch.int32, device=dev)
     da, dc = torch.from_numpy(a2bl).to(dev), torch.from_numpy(conj).to(dev)
     ms = timeit(lambda: ops.reorder(vis, ro, da, dc, NSTAND, NPOL, nchan, wpc), 4)
@@ -310,8 +317,7 @@ def path_kernels(torch, ops, dev, nchan, hbm_peak, iters=10):
     xc = ops.XCorr(nstand=NSTAND, npol=NPOL, nchan=nchan, ntime_gulp=ntime)
     gulps = [torch.randint(0, 256, (ntime, nchan, NINPUT), dtype=torch.uint8, device=dev) for _ in range(4)]
     acc2 = torch.zeros(nw, dtype=torch.int32, device=dev)
-    sel = np.random.default_rng(1).integers(0, a2bl.size, 4704)
-    xc.set_subsel(a2bl.reshape(-1)[sel].copy(), conj.reshape(-1)[sel].copy(), 4)
+    xc.set_subsel(real_vm, real_cj, 4)
     fast = torch.zeros((nchan // 4, 4704, 2), dtype=torch.int32, device=dev)
     k = [0]
 

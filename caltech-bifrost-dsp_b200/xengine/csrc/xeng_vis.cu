@@ -55,16 +55,48 @@ __global__ void __launch_bounds__(256) subsel_kernel(const int32_t* __restrict__
                                                      const int32_t* __restrict__ vismap,
                                                      const int32_t* __restrict__ conj, int nvis, int nchan_out,
                                                      int nchan_sum, long W, long plane_words) {
-  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  const int v0 = blockIdx.x * blockDim.x + threadIdx.x;
   const int co = blockIdx.y;
-  if (v >= nvis || co >= nchan_out) return;
+  if (co >= nchan_out) return;
+  const bool live = v0 < nvis;
+  const int v = live ? v0 : nvis - 1;                  // idle lanes shadow the last entry: the warp stays whole
   const long idx = vismap[v];
-  const int32_t* p = in + static_cast<long>(co) * nchan_sum * W + idx;
+  // The four pol products of a stand pair are one 16-byte cell, and a real selection (CorrSubsel's 48 x 49 / 2 stand
+  // pairs x 4 products, corr_subsel_block.py:185) takes whole cells on neighbouring entries: the lanes of a warp
+  // that want words of the same cell elect one of them to read it -- one 128-bit load per (cell, channel, plane)
+  // instead of up to four 32-bit loads that each cost a full DRAM sector.
+  const long cell = idx >> 2;
+  const unsigned peers = __match_any_sync(0xffffffffu, cell);
+  const int leader = __ffs(peers) - 1;
+  const bool aligned = ((reinterpret_cast<uintptr_t>(in) | (static_cast<unsigned long>(W) << 2) |
+                         (static_cast<unsigned long>(plane_words) << 2)) & 15) == 0;
   int re = 0, im = 0;
-  for (int k = 0; k < nchan_sum; ++k) {
-    re += __ldg(p + k * W);
-    im += __ldg(p + plane_words + k * W);
+  if (aligned) {
+    int4 r4 = make_int4(0, 0, 0, 0), i4 = make_int4(0, 0, 0, 0);
+    if ((threadIdx.x & 31) == leader) {
+      const int32_t* p = in + static_cast<long>(co) * nchan_sum * W + cell * 4;
+      for (int k = 0; k < nchan_sum; ++k) {
+        const int4 a = __ldg(reinterpret_cast<const int4*>(p + k * W));
+        const int4 b = __ldg(reinterpret_cast<const int4*>(p + plane_words + k * W));
+        r4.x += a.x; r4.y += a.y; r4.z += a.z; r4.w += a.w;
+        i4.x += b.x; i4.y += b.y; i4.z += b.z; i4.w += b.w;
+      }
+    }
+    r4.x = __shfl_sync(0xffffffffu, r4.x, leader); r4.y = __shfl_sync(0xffffffffu, r4.y, leader);
+    r4.z = __shfl_sync(0xffffffffu, r4.z, leader); r4.w = __shfl_sync(0xffffffffu, r4.w, leader);
+    i4.x = __shfl_sync(0xffffffffu, i4.x, leader); i4.y = __shfl_sync(0xffffffffu, i4.y, leader);
+    i4.z = __shfl_sync(0xffffffffu, i4.z, leader); i4.w = __shfl_sync(0xffffffffu, i4.w, leader);
+    const int w4 = static_cast<int>(idx & 3);
+    re = w4 == 0 ? r4.x : w4 == 1 ? r4.y : w4 == 2 ? r4.z : r4.w;
+    im = w4 == 0 ? i4.x : w4 == 1 ? i4.y : w4 == 2 ? i4.z : i4.w;
+  } else {
+    const int32_t* p = in + static_cast<long>(co) * nchan_sum * W + idx;
+    for (int k = 0; k < nchan_sum; ++k) {
+      re += __ldg(p + k * W);
+      im += __ldg(p + plane_words + k * W);
+    }
   }
+  if (!live) return;
   if (conj[v]) im = -im;
   if (LAYOUT == 0) out[static_cast<long>(co) * nvis + v] = make_int2(re, im);
   if (LAYOUT == 1) out[(static_cast<long>(v >> 2) * nchan_out + co) * 4 + (v & 3)] = make_int2(re, im);
