@@ -67,7 +67,9 @@ def full(src, dst):
         for r in data:
             f.write("== %s (ID %s)\n" % (r[name_col][:80], r[0]))
             for i, h in enumerate(hdr):
-                if h in KEYS or "tensor" in h or "tmem" in h:    # every tensor-pipe / TMEM counter the report holds
+                tensorish = ("pipe_tensor" in h or "mem_tensor" in h or "pipe_tmem" in h) and h.endswith(
+                    ("pct_of_peak_sustained_elapsed", "pct_of_peak_sustained_active", "_realtime.avg", ".sum")) and ".m" not in h[-40:-30]
+                if h in KEYS or tensorish:          # the tensor-pipe / TMEM counters the report holds
                     f.write("  %-80s %s %s\n" % (h, r[i], units[i]))
     sys.stdout.write(open(dst).read())
     # steady-state (accumulating) launch = the one that also reads the accumulator: DRAM bytes per launch for bench.py
