@@ -19,9 +19,13 @@
 //   GEMM     per (channel c, 128 time samples): D[128 t x N] = A[128 x K] * B[N x K]^T,
 //            K = 2 ninput stacked [re | im], N = 3 digits x 2 (re, im) x nb beams (192 for 32 beams), B rows
 //                out_re(b): [ w_re | -w_im ]      out_im(b): [ w_im | w_re ]
-//   A        lives in TENSOR MEMORY (tcgen05.mma with the A operand in TMEM, K-major): unpack warps load a thread's 64
-//            raw bytes (64 inputs of its time sample) straight from global memory, sign-extend the nibbles with SWAR
-//            arithmetic and tcgen05.st them as 16 + 16 columns (re | im); the voltages never touch shared memory.
+//   A        lives in TENSOR MEMORY (tcgen05.mma with the A operand in TMEM, K-major).  The producer warp brings RAW
+//            4+4-bit boxes {64 inputs, 1 channel, 128 samples} into an 8-deep shared-memory ring with TMA
+//            (SWIZZLE_64B; a thread reading its own sample's 64 bytes straight from global memory costs a warp 32
+//            sector requests per 16-byte load -- the first version of this kernel was L1-request bound on exactly
+//            that); an unpack thread takes its sample's row with four conflict-free LDS.128, sign-extends the
+//            nibbles with SWAR arithmetic and tcgen05.st's them as 16 + 16 columns (re | im).  The UNPACKED voltages
+//            never touch shared memory.
 //   B        digit planes are precomputed in global memory in exactly the K-major no-swizzle core-matrix layout the
 //            MMA reads ([n/8][k/16][n%8][16 B] per 32-deep K-block), so one stage (64 inputs = 4 MMAs) is ONE 1-D
 //            bulk copy (cp.async.bulk, 24 KB) into a 4-deep shared-memory ring.
@@ -32,9 +36,11 @@
 //            ntime_sum samples in time order (beamform_sum_beams_block.py:245; beamformer_sum_test.py:64-77) --
 //            the same expressions and order as beam_integrate_kernel, so both paths agree bit for bit.
 //
-// Roles (576 threads): warps 0-3 epilogue, 4-15 unpack (3 groups x 4 lane quarters, a group per stage, the next
-// stage's bytes prefetched into registers), 16 bulk-copy producer, 17 MMA issuer.  Persistent grid, one CTA per SM,
+// Roles (576 threads): warps 0-3 epilogue, 4-15 unpack (3 groups x 4 lane quarters, a group per stage), 16 producer
+// (raw TMA boxes + digit-plane bulk copies), 17 MMA issuer.  Persistent grid, one CTA per SM,
 // tiles ordered (beam block, channel, time tile) so the CTAs working at one moment share a channel's digits in L2.
+#include <cuda.h>
+
 #include "xeng_ptx.cuh"
 #include "xeng_internal.h"
 
@@ -53,8 +59,11 @@ constexpr int BT_WARP_PROD = BT_EPI_WARPS + BT_UNPACK_WARPS, BT_WARP_MMA = BT_WA
 constexpr int BT_THREADS = (BT_WARP_MMA + 1) * 32;
 constexpr int BT_STAGE_MAX = 6 * BT_NB_MAX * 2 * BT_KIN;          // 24576 B: N rows x 128 K-bytes
 constexpr int BT_HDR = 1024;
+constexpr int BT_RAW_SLOTS = 8;                                   // raw ring depth: 64 KB of voltages in flight per SM
+constexpr int BT_RAW_BYTES = BT_M * BT_KIN;                       // 8 KB: [128 samples][64 inputs], 64B-swizzled
 constexpr int BT_PROD_BYTES = (BT_NB_MAX / 2) * 4 * BT_M * 4;     // 32 KB: [pair][component][sample] floats
-constexpr int BT_SMEM = BT_HDR + BT_SLOTS * BT_STAGE_MAX + BT_PROD_BYTES + 1024;
+constexpr int BT_SMEM = BT_HDR + BT_RAW_SLOTS * BT_RAW_BYTES + BT_SLOTS * BT_STAGE_MAX + BT_PROD_BYTES + 1024;
+static_assert(BT_SMEM <= 232448, "shared memory budget");
 static_assert(BT_A_COL0 + BT_SLOTS * BT_ACOLS <= 512, "TMEM budget");
 
 struct BtHdr {
@@ -62,6 +71,8 @@ struct BtHdr {
   uint64_t empty[BT_SLOTS];      // the MMAs reading the slot have completed (tcgen05.commit)
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
+  uint64_t raw_full[BT_RAW_SLOTS];    // TMA box landed
+  uint64_t raw_empty[BT_RAW_SLOTS];   // the 4 unpack warps of the stage have read it
   uint32_t tmem_base;
 };
 
@@ -84,11 +95,12 @@ __device__ __forceinline__ float digit_sum_to_float(uint32_t d) {
 }
 
 template <bool FUSED>
-__global__ void __launch_bounds__(BT_THREADS, 1) beamform_tc_kernel(BeamTcArgs a) {
+__global__ void __launch_bounds__(BT_THREADS, 1) beamform_tc_kernel(const __grid_constant__ CUtensorMap tmap, BeamTcArgs a) {
   extern __shared__ uint8_t bt_smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(bt_smem_raw) + 1023) & ~uintptr_t(1023));
   BtHdr* S = reinterpret_cast<BtHdr*>(smem);
-  uint8_t* bst = smem + BT_HDR;
+  uint8_t* rawring = smem + BT_HDR;
+  uint8_t* bst = rawring + BT_RAW_SLOTS * BT_RAW_BYTES;
   float* prod = reinterpret_cast<float*>(bst + BT_SLOTS * BT_STAGE_MAX);
 
   const int warp = static_cast<int>(__reduce_min_sync(0xffffffffu, threadIdx.x >> 5));
@@ -105,12 +117,17 @@ __global__ void __launch_bounds__(BT_THREADS, 1) beamform_tc_kernel(BeamTcArgs a
       mbar_init(&S->tmem_full[b], 1);
       mbar_init(&S->tmem_empty[b], BT_EPI_WARPS * 32);
     }
+    for (int s = 0; s < BT_RAW_SLOTS; ++s) {
+      mbar_init(&S->raw_full[s], 1);
+      mbar_init(&S->raw_empty[s], 4);
+    }
     mbar_fence_init();
   }
   if (warp == BT_WARP_MMA) {
     tmem_alloc(&S->tmem_base, 512);
     tmem_relinquish();
   }
+  if (warp == BT_WARP_PROD && lane == 0) tma_prefetch_desc(&tmap);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -183,31 +200,21 @@ __global__ void __launch_bounds__(BT_THREADS, 1) beamform_tc_kernel(BeamTcArgs a
       }
     }
   } else if (warp < BT_WARP_PROD) {
-    // ===================================================================== unpack: global -> registers -> TMEM
+    // ===================================================================== unpack: raw ring -> registers -> TMEM
     const int u = warp - BT_EPI_WARPS, q = u & 3, g = u >> 2;
     const int m = q * 32 + lane;
     const uint32_t a_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + BT_A_COL0;
-    auto load = [&](int gs, uint4 (&raw)[4]) -> bool {
-      const int it = gs / a.nst, s = gs - it * a.nst;
-      const long tile = static_cast<long>(blockIdx.x) + static_cast<long>(it) * gridDim.x;
-      raw[0] = raw[1] = raw[2] = raw[3] = make_uint4(0u, 0u, 0u, 0u);
-      if (tile >= a.ntiles) return false;
-      const int tl = static_cast<int>(tile);
-      const int tt = tl % a.ntt, c = (tl / a.ntt) % a.nchan;
-      const int t = tt * a.tile_t + m;
-      if (m < a.tile_t && t < a.nt_valid) {
-        const uint8_t* p = a.in + (static_cast<long>(t) * a.nchan + c) * a.ninput + s * BT_KIN;
+    // row m of a 64B-swizzled box: logical 16-byte chunk j sits at chunk j ^ ((m >> 1) & 3)
+    const uint32_t row_addr = smem_u32(rawring) + m * BT_KIN, sw = (m >> 1) & 3;
+    const int nstage_total = ((a.ntiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
+                              static_cast<int>(gridDim.x)) * a.nst;      // stages this CTA runs
+    for (int gs = g; gs < nstage_total; gs += BT_GROUPS) {
+      const int rs = gs % BT_RAW_SLOTS;
+      mbar_wait(&S->raw_full[rs], (gs / BT_RAW_SLOTS) & 1, nullptr, 600 + rs);
+      const uint32_t base = row_addr + rs * BT_RAW_BYTES;
+      uint4 cur[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (s * BT_KIN + 16 * j < a.ninput) raw[j] = ldg_nc_v4(p + 16 * j);
-      }
-      return true;
-    };
-    uint4 cur[4], nxt[4];
-    int gs = g;
-    bool ok = load(gs, cur);
-    while (ok) {
-      const bool ok2 = load(gs + BT_GROUPS, nxt);          // next stage's bytes are in flight while this one is unpacked
+      for (int j = 0; j < 4; ++j) cur[j] = lds_v4(base + ((j ^ sw) << 4));
       uint32_t r[32];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -216,6 +223,9 @@ __global__ void __launch_bounds__(BT_THREADS, 1) beamform_tc_kernel(BeamTcArgs a
         r[4 * j + 2] = unpack_re4(cur[j].z); r[16 + 4 * j + 2] = unpack_im4(cur[j].z);
         r[4 * j + 3] = unpack_re4(cur[j].w); r[16 + 4 * j + 3] = unpack_im4(cur[j].w);
       }
+      // the unpacked words depend on every byte loaded: once they exist the raw slot may be refilled
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&S->raw_empty[rs]);
       const int slot = gs % BT_SLOTS;
       mbar_wait(&S->empty[slot], ((gs / BT_SLOTS) & 1) ^ 1, nullptr, 200 + slot);
       tc_fence_after();
@@ -224,25 +234,42 @@ __global__ void __launch_bounds__(BT_THREADS, 1) beamform_tc_kernel(BeamTcArgs a
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&S->full[slot]);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) cur[j] = nxt[j];
-      ok = ok2;
-      gs += BT_GROUPS;
     }
   } else if (warp == BT_WARP_PROD) {
-    // ===================================================================== digit-plane producer (one lane)
+    // ===================================================================== producer (one lane): raw boxes + digit planes
     if (lane == 0) {
-      int gs = 0;
-      for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
-        const int cb = tile / a.ntt;                       // = bb * nchan + c: digit planes are stored [c][bb]
+      // Two rings of different depth fed by one thread: the raw ring runs ahead of the digit ring, so raw boxes are
+      // issued first for as many stages as their ring has room, then the digit stage that is due.
+      int gs_raw = 0, gs_dig = 0;
+      int tile_raw = blockIdx.x, s_raw = 0, tile_dig = blockIdx.x, s_dig = 0;
+      while (tile_dig < a.ntiles) {
+        // raw boxes: up to BT_RAW_SLOTS - 1 stages ahead of the digit ring, never blocking while a digit stage is due
+        while (tile_raw < a.ntiles && gs_raw < gs_dig + BT_RAW_SLOTS) {
+          const int rs = gs_raw % BT_RAW_SLOTS;
+          if (gs_raw >= BT_RAW_SLOTS && !mbar_try_wait(&S->raw_empty[rs], ((gs_raw / BT_RAW_SLOTS) & 1) ^ 1)) {
+            if (gs_raw > gs_dig) break;                                   // not free yet: go feed the digit ring
+            mbar_wait(&S->raw_empty[rs], ((gs_raw / BT_RAW_SLOTS) & 1) ^ 1, nullptr, 700 + rs);
+          }
+          const int tt = tile_raw % a.ntt, c = (tile_raw / a.ntt) % a.nchan;
+          mbar_arrive_expect_tx(&S->raw_full[rs], BT_RAW_BYTES);
+          tma_load_3d(smem_u32(rawring + rs * BT_RAW_BYTES), &tmap, &S->raw_full[rs], s_raw * BT_KIN, c, tt * a.tile_t);
+          ++gs_raw;
+          if (++s_raw == a.nst) {
+            s_raw = 0;
+            tile_raw += gridDim.x;
+          }
+        }
+        const int cb = tile_dig / a.ntt;                                  // = bb * nchan + c: digit planes are stored [c][bb]
         const int c = cb % a.nchan, bb = cb / a.nchan;
-        const int8_t* src = a.wdig + (static_cast<long>(c) * a.nbb + bb) * a.nst * stage_bytes;
-        for (int s = 0; s < a.nst; ++s, ++gs) {
-          const int slot = gs % BT_SLOTS;
-          mbar_wait(&S->empty[slot], ((gs / BT_SLOTS) & 1) ^ 1, nullptr, 300 + slot);
-          mbar_arrive_expect_tx(&S->full[slot], stage_bytes);
-          bulk_load(smem_u32(bst + slot * BT_STAGE_MAX), src + static_cast<long>(s) * stage_bytes, stage_bytes,
-                    &S->full[slot]);
+        const int8_t* src = a.wdig + ((static_cast<long>(c) * a.nbb + bb) * a.nst + s_dig) * stage_bytes;
+        const int slot = gs_dig % BT_SLOTS;
+        mbar_wait(&S->empty[slot], ((gs_dig / BT_SLOTS) & 1) ^ 1, nullptr, 300 + slot);
+        mbar_arrive_expect_tx(&S->full[slot], stage_bytes);
+        bulk_load(smem_u32(bst + slot * BT_STAGE_MAX), src, stage_bytes, &S->full[slot]);
+        ++gs_dig;
+        if (++s_dig == a.nst) {
+          s_dig = 0;
+          tile_dig += gridDim.x;
         }
       }
     }
@@ -294,40 +321,40 @@ __device__ __forceinline__ float scale_pow2(float x, int k) {
   return x * __int_as_float((k1 + 127) << 23) * __int_as_float((k2 + 127) << 23);
 }
 
-constexpr int WD_THREADS = 128;            // 32 chunks (512 inputs) x 4 beams per pass
+constexpr int WD_THREADS = 128;
+constexpr int WD_CHUNK_F2 = 18;            // a 16-input chunk (16 float2 = 128 B) padded to 144 B: conflict-free LDS.128
 __global__ void __launch_bounds__(WD_THREADS) beam_weight_digits_kernel(const float2* __restrict__ w, int8_t* __restrict__ dig,
                                                                         float* __restrict__ scale, int nchan, int nbeam,
                                                                         int ninput, int nb, int nbb, int nst) {
+  extern __shared__ __align__(16) float2 wtile[];          // [4 beams][nchunk][WD_CHUNK_F2]
   __shared__ int smax[4];                  // per beam: max |component| as float bits (non-negative floats order as ints)
   __shared__ int sbad;
   const int c = blockIdx.x, quad = blockIdx.y;
-  const int tid = threadIdx.x, bq = tid & 3;
-  const int bg = quad * 4 + bq, bb = bg / nb, bl = bg - bb * nb;      // padded beam index, its block, index in block
-  const bool beam_ok = bg < nbeam;         // padded beams of the last block: zero rows
-  const float2* wrow = w + (static_cast<long>(c) * nbeam + bg) * ninput;
-  const int nchunk = nst * 4;
+  const int tid = threadIdx.x;
+  const int nchunk = nst * 4, row_f2 = nchunk * WD_CHUNK_F2;
   if (tid < 4) smax[tid] = 0;
   if (tid == 0) sbad = 0;
+  for (int i = tid; i < 4 * row_f2; i += WD_THREADS) wtile[i] = make_float2(0.f, 0.f);   // K padding, padded beams
   __syncthreads();
-  // ---- pass 1: row maxima
-  float mx = 0.f;
-  bool bad = false;
-  for (int chunk = tid >> 2; chunk < nchunk; chunk += WD_THREADS / 4) {
-    const int i0 = 16 * chunk;
-    if (!beam_ok || i0 >= ninput) continue;
-#pragma unroll
-    for (int k = 0; k < 16; k += 2) {      // ninput % 16 == 0: a chunk is all inside or all outside
-      const float4 v = __ldg(reinterpret_cast<const float4*>(wrow + i0 + k));
-      const float a0 = fabsf(v.x), a1 = fabsf(v.y), a2 = fabsf(v.z), a3 = fabsf(v.w);
-      bad |= !(a0 <= 3.0e38f) || !(a1 <= 3.0e38f) || !(a2 <= 3.0e38f) || !(a3 <= 3.0e38f);   // inf / nan
-      mx = fmaxf(mx, fmaxf(fmaxf(a0, a1), fmaxf(a2, a3)));
-    }
+  // ---- pass 1: the four weight rows into shared memory with coalesced 16-byte loads (a warp reads 512 contiguous
+  // bytes), row maxima on the way
+  const int f4_per_row = ninput / 2;
+  for (int idx = tid; idx < 4 * f4_per_row; idx += WD_THREADS) {
+    const int bq = idx / f4_per_row, pair = idx - bq * f4_per_row, i = 2 * pair;
+    const int bg = quad * 4 + bq;
+    if (bg >= nbeam) continue;
+    const float4 v = __ldg(reinterpret_cast<const float4*>(w + (static_cast<long>(c) * nbeam + bg) * ninput + i));
+    *reinterpret_cast<float4*>(&wtile[bq * row_f2 + (i >> 4) * WD_CHUNK_F2 + (i & 15)]) = v;
+    const float a0 = fabsf(v.x), a1 = fabsf(v.y), a2 = fabsf(v.z), a3 = fabsf(v.w);
+    if (!(a0 <= 3.0e38f) || !(a1 <= 3.0e38f) || !(a2 <= 3.0e38f) || !(a3 <= 3.0e38f)) atomicOr(&sbad, 1 << bq);   // inf / nan
+    atomicMax(&smax[bq], __float_as_int(fmaxf(fmaxf(a0, a1), fmaxf(a2, a3))));
   }
-  atomicMax(&smax[bq], __float_as_int(mx));
-  if (bad) atomicOr(&sbad, 1 << bq);       // inf / nan weights poison their whole row, as they would in fp32
   __syncthreads();
-  mx = __int_as_float(smax[bq]);
-  const bool rowbad = (sbad >> bq) & 1;
+  // ---- pass 2: thread (chunk, bq) quantises and splits its 16 inputs, writes 32 contiguous bytes per digit block
+  const int bq = tid & 3;
+  const int bg = quad * 4 + bq, bb = bg / nb, bl = bg - bb * nb;      // padded beam index, its block, index in block
+  const float mx = __int_as_float(smax[bq]);
+  const bool rowbad = (sbad >> bq) & 1;    // inf / nan weights poison their whole row, as they would in fp32
   int e = 0;
   if (mx > 0.f) {
     const float fr = frexpf(mx, &e);       // mx = fr * 2^e, fr in [0.5, 1)
@@ -335,34 +362,36 @@ __global__ void __launch_bounds__(WD_THREADS) beam_weight_digits_kernel(const fl
   }
   if (tid < 4)
     scale[(static_cast<long>(c) * nbb + bb) * BT_NB_MAX + bl] = rowbad ? __int_as_float(0x7fc00000) : scale_pow2(1.0f, e - 23);
-  // ---- pass 2: quantise, split, store (the row is in L1 / L2 from pass 1)
   const int N = 6 * nb;
-  const bool aligned = (reinterpret_cast<uintptr_t>(w) & 15) == 0;
   for (int chunk = tid >> 2; chunk < nchunk; chunk += WD_THREADS / 4) {
-    const int i0 = 16 * chunk;
     uint32_t pre[3][4], pim[3][4], pnim[3][4];               // 16 digit bytes each: w_re, w_im, -w_im
 #pragma unroll
     for (int gdig = 0; gdig < 3; ++gdig)
 #pragma unroll
       for (int j = 0; j < 4; ++j) pre[gdig][j] = pim[gdig][j] = pnim[gdig][j] = 0u;
-    if (beam_ok && i0 < ninput && !rowbad) {
+    if (!rowbad) {
+      const float4* src = reinterpret_cast<const float4*>(&wtile[bq * row_f2 + chunk * WD_CHUNK_F2]);
 #pragma unroll
-      for (int k = 0; k < 16; ++k) {
-        const float2 x = __ldg(wrow + i0 + k);
-        const int wr = __float2int_rn(scale_pow2(x.x, 23 - e)), wi = __float2int_rn(scale_pow2(x.y, 23 - e));
-        int dr[3], di[3], dn[3];
-        split_digits(wr, dr);
-        split_digits(wi, di);
-        split_digits(-wi, dn);
+      for (int k2 = 0; k2 < 8; ++k2) {
+        const float4 x2 = src[k2];
+        const float xs[4] = {x2.x, x2.y, x2.z, x2.w};
 #pragma unroll
-        for (int gdig = 0; gdig < 3; ++gdig) {
-          pre[gdig][k >> 2] |= static_cast<uint32_t>(dr[gdig] & 0xFF) << (8 * (k & 3));
-          pim[gdig][k >> 2] |= static_cast<uint32_t>(di[gdig] & 0xFF) << (8 * (k & 3));
-          pnim[gdig][k >> 2] |= static_cast<uint32_t>(dn[gdig] & 0xFF) << (8 * (k & 3));
+        for (int h = 0; h < 2; ++h) {
+          const int k = 2 * k2 + h;
+          const int wr = __float2int_rn(scale_pow2(xs[2 * h], 23 - e)), wi = __float2int_rn(scale_pow2(xs[2 * h + 1], 23 - e));
+          int dr[3], di[3], dn[3];
+          split_digits(wr, dr);
+          split_digits(wi, di);
+          split_digits(-wi, dn);
+#pragma unroll
+          for (int gdig = 0; gdig < 3; ++gdig) {
+            pre[gdig][k >> 2] |= static_cast<uint32_t>(dr[gdig] & 0xFF) << (8 * (k & 3));
+            pim[gdig][k >> 2] |= static_cast<uint32_t>(di[gdig] & 0xFF) << (8 * (k & 3));
+            pnim[gdig][k >> 2] |= static_cast<uint32_t>(dn[gdig] & 0xFF) << (8 * (k & 3));
+          }
         }
       }
     }
-    (void)aligned;
     const int s = chunk >> 2, kq = chunk & 3;                // stage, 16-input chunk inside the stage
     const int jre = kq >> 1, jim = 2 + (kq >> 1), k16 = kq & 1;
     int8_t* stage = dig + ((static_cast<long>(c) * nbb + bb) * nst + s) * (static_cast<long>(N) * 2 * BT_KIN);
@@ -406,7 +435,12 @@ cudaError_t launch_beam_weight_digits(const float2* w, int8_t* dig, float* scale
   if (!beam_tc_geometry(ninput, nchan, nbeam, &g)) return cudaErrorInvalidValue;
   if (reinterpret_cast<uintptr_t>(w) & 15) return cudaErrorInvalidValue;     // float4 loads of the weight rows
   dim3 grid(nchan, g.nbb * g.nb / 4);
-  beam_weight_digits_kernel<<<grid, WD_THREADS, 0, stream>>>(w, dig, scale, nchan, nbeam, ninput, g.nb, g.nbb, g.nst);
+  const size_t smem = static_cast<size_t>(4) * g.nst * 4 * WD_CHUNK_F2 * sizeof(float2);     // <= 73.7 KB (ninput 2032)
+  cudaError_t ce = configure_once_per_device([]() -> cudaError_t {
+    return cudaFuncSetAttribute(beam_weight_digits_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024);
+  }, kCfgBeamDigits);
+  if (ce != cudaSuccess) return ce;
+  beam_weight_digits_kernel<<<grid, WD_THREADS, smem, stream>>>(w, dig, scale, nchan, nbeam, ninput, g.nb, g.nbb, g.nst);
   return cudaGetLastError();
 }
 
@@ -439,8 +473,22 @@ cudaError_t launch_beamform_tc(const BeamArgs& b, const int8_t* dig, const float
   if (ntiles > 0x7fffffffL) return cudaErrorInvalidValue;
   a.ntiles = static_cast<int>(ntiles);
   const int grid = a.ntiles < nsm ? a.ntiles : nsm;
-  if (b.pow_out) beamform_tc_kernel<true><<<grid, BT_THREADS, BT_SMEM, stream>>>(a);
-  else beamform_tc_kernel<false><<<grid, BT_THREADS, BT_SMEM, stream>>>(a);
+  TensorMapEncodeFn encode = nullptr;
+  e = tensor_map_encoder(&encode);
+  if (e != cudaSuccess) return e;
+  alignas(64) CUtensorMap tmap;
+  const cuuint64_t gdim[3] = {static_cast<cuuint64_t>(a.ninput), static_cast<cuuint64_t>(a.nchan),
+                              static_cast<cuuint64_t>(a.nt_valid)};       // rows past nt_valid read as zero
+  const cuuint64_t gstride[2] = {static_cast<cuuint64_t>(a.ninput),
+                                 static_cast<cuuint64_t>(a.ninput) * static_cast<cuuint64_t>(a.nchan)};
+  const cuuint32_t box[3] = {BT_KIN, 1, BT_M};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<uint8_t*>(a.in), gdim, gstride, box, estr,
+                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
+  if (b.pow_out) beamform_tc_kernel<true><<<grid, BT_THREADS, BT_SMEM, stream>>>(tmap, a);
+  else beamform_tc_kernel<false><<<grid, BT_THREADS, BT_SMEM, stream>>>(tmap, a);
   return cudaGetLastError();
 }
 

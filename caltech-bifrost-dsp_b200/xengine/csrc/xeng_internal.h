@@ -9,7 +9,7 @@ namespace xeng {
 // Per-device one-time configuration (cudaFuncSetAttribute, __constant__ tables): function attributes and constant
 // memory belong to the device's context, so a process that holds handles on several GPUs must configure each one.
 // `fn` runs once per (key, current device), under a lock (two block threads may make their first launch together).
-enum CfgKey { kCfgCorrSwz = 0, kCfgCorrTc, kCfgBeam, kCfgBeamTc, kCfgCount };
+enum CfgKey { kCfgCorrSwz = 0, kCfgCorrTc, kCfgBeam, kCfgBeamTc, kCfgBeamDigits, kCfgCount };
 constexpr int kCfgMaxDevices = 64;
 template <class F>
 inline cudaError_t configure_once_per_device(F&& fn, int key) {
@@ -25,6 +25,27 @@ inline cudaError_t configure_once_per_device(F&& fn, int key) {
   if (e == cudaSuccess) done[key][dev] = true;
   return e;
 }
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point lookup (no -lcuda): process-wide, fetched once
+#ifdef CUDA_VERSION
+typedef CUresult (*TensorMapEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                      const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                      CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+inline cudaError_t tensor_map_encoder(TensorMapEncodeFn* out) {
+  static TensorMapEncodeFn encode = nullptr;
+  static std::once_flag once;
+  static cudaError_t err = cudaSuccess;
+  std::call_once(once, []() {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    err = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (err == cudaSuccess && (qres != cudaDriverEntryPointSuccess || !fn)) err = cudaErrorNotSupported;
+    if (err == cudaSuccess) encode = reinterpret_cast<TensorMapEncodeFn>(fn);
+  });
+  *out = encode;
+  return err;
+}
+#endif
 
 struct CorrArgs {
   const uint8_t* in;    // [ntime][nchan][ninput] 4+4-bit complex
