@@ -49,26 +49,31 @@ namespace {
 
 constexpr int BT_M = 128;                    // time samples per tile (TMEM lanes)
 constexpr int BT_KIN = 64;                   // inputs per stage: 4 MMAs of K = 32 (re 0-31, re 32-63, im 0-31, im 32-63)
-constexpr int BT_SLOTS = 4;                  // stage ring depth (A in TMEM, B in shared memory)
+constexpr int BT_SLOTS = 4;                  // A-stage ring depth (TMEM columns 384..511)
+constexpr int BT_BSLOTS = 6;                 // digit-plane (B) ring depth in shared memory: an L2 -> SM bulk copy takes
+                                             // ~1300 cycles to land against 384 cycles of MMAs per stage
 constexpr int BT_ACOLS = 32;                 // TMEM columns of one A stage: 16 re + 16 im
 constexpr int BT_DCOLS = 192;                // column stride between the two accumulators
 constexpr int BT_A_COL0 = 2 * BT_DCOLS;      // 384: A stages live in columns 384..511
 constexpr int BT_NB_MAX = 32;                // beams per beam block
 constexpr int BT_EPI_WARPS = 4, BT_GROUPS = 3, BT_UNPACK_WARPS = 4 * BT_GROUPS;
-constexpr int BT_WARP_PROD = BT_EPI_WARPS + BT_UNPACK_WARPS, BT_WARP_MMA = BT_WARP_PROD + 1;
+constexpr int BT_WARP_PROD = BT_EPI_WARPS + BT_UNPACK_WARPS, BT_WARP_RAW = BT_WARP_PROD + 1, BT_WARP_MMA = BT_WARP_RAW + 1;
 constexpr int BT_THREADS = (BT_WARP_MMA + 1) * 32;
 constexpr int BT_STAGE_MAX = 6 * BT_NB_MAX * 2 * BT_KIN;          // 24576 B: N rows x 128 K-bytes
-constexpr int BT_HDR = 1024;
-constexpr int BT_RAW_SLOTS = 8;                                   // raw ring depth: 64 KB of voltages in flight per SM
+constexpr int BT_HDR = 4096;                                      // barriers + one scratch word per unpack thread
+constexpr int BT_SCRATCH_OFF = 1024;
+constexpr int BT_RAW_SLOTS = 6;                                   // raw ring depth: 48 KB of voltages in flight per SM
 constexpr int BT_RAW_BYTES = BT_M * BT_KIN;                       // 8 KB: [128 samples][64 inputs], 64B-swizzled
-constexpr int BT_PROD_BYTES = (BT_NB_MAX / 2) * 4 * BT_M * 4;     // 32 KB: [pair][component][sample] floats
-constexpr int BT_SMEM = BT_HDR + BT_RAW_SLOTS * BT_RAW_BYTES + BT_SLOTS * BT_STAGE_MAX + BT_PROD_BYTES + 1024;
+constexpr int BT_PROD_BYTES = 4 * 4 * BT_M * 4;                   // 8 KB: [4 pairs][component][sample] floats
+constexpr int BT_SMEM = BT_HDR + BT_RAW_SLOTS * BT_RAW_BYTES + BT_BSLOTS * BT_STAGE_MAX + BT_PROD_BYTES + 1024;
 static_assert(BT_SMEM <= 232448, "shared memory budget");
 static_assert(BT_A_COL0 + BT_SLOTS * BT_ACOLS <= 512, "TMEM budget");
 
 struct BtHdr {
-  uint64_t full[BT_SLOTS];       // A stage written (4 unpack warps) + B stage landed (producer's expect_tx)
-  uint64_t empty[BT_SLOTS];      // the MMAs reading the slot have completed (tcgen05.commit)
+  uint64_t full[BT_SLOTS];       // A stage written to TMEM (4 unpack warps)
+  uint64_t empty[BT_SLOTS];      // the MMAs reading the A slot have completed (tcgen05.commit)
+  uint64_t b_full[BT_BSLOTS];    // digit-plane stage landed (expect_tx)
+  uint64_t b_empty[BT_BSLOTS];   // the MMAs reading the B slot have completed (tcgen05.commit)
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
   uint64_t raw_full[BT_RAW_SLOTS];    // TMA box landed
@@ -101,7 +106,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) beamform_tc_kernel(const __grid
   BtHdr* S = reinterpret_cast<BtHdr*>(smem);
   uint8_t* rawring = smem + BT_HDR;
   uint8_t* bst = rawring + BT_RAW_SLOTS * BT_RAW_BYTES;
-  float* prod = reinterpret_cast<float*>(bst + BT_SLOTS * BT_STAGE_MAX);
+  float* prod = reinterpret_cast<float*>(bst + BT_BSLOTS * BT_STAGE_MAX);
 
   const int warp = static_cast<int>(__reduce_min_sync(0xffffffffu, threadIdx.x >> 5));
   const int lane = threadIdx.x & 31;
@@ -110,8 +115,12 @@ __global__ void __launch_bounds__(BT_THREADS, 1) beamform_tc_kernel(const __grid
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < BT_SLOTS; ++s) {
-      mbar_init(&S->full[s], 4 + 1);
+      mbar_init(&S->full[s], 4);
       mbar_init(&S->empty[s], 1);
+    }
+    for (int s = 0; s < BT_BSLOTS; ++s) {
+      mbar_init(&S->b_full[s], 1);
+      mbar_init(&S->b_empty[s], 1);
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&S->tmem_full[b], 1);
@@ -119,7 +128,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) beamform_tc_kernel(const __grid
     }
     for (int s = 0; s < BT_RAW_SLOTS; ++s) {
       mbar_init(&S->raw_full[s], 1);
-      mbar_init(&S->raw_empty[s], 4);
+      mbar_init(&S->raw_empty[s], 4 * 32);
     }
     mbar_fence_init();
   }
@@ -127,7 +136,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) beamform_tc_kernel(const __grid
     tmem_alloc(&S->tmem_base, 512);
     tmem_relinquish();
   }
-  if (warp == BT_WARP_PROD && lane == 0) tma_prefetch_desc(&tmap);
+  if (warp == BT_WARP_RAW && lane == 0) tma_prefetch_desc(&tmap);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -172,31 +181,30 @@ __global__ void __launch_bounds__(BT_THREADS, 1) beamform_tc_kernel(const __grid
             }
           }
         } else {
+          // per 8-beam chunk: the 4 dual-pol beams' per-sample products go to shared memory, then ntime_sum of them
+          // are summed in time order (same expressions and order as beam_integrate_kernel)
 #pragma unroll
           for (int p = 0; p < 4; ++p) {
             const float4 pr = beam_products(make_float2(v[4 * p], v[4 * p + 1]), make_float2(v[4 * p + 2], v[4 * p + 3]));
-            float* dst = prod + ((ch * 4 + p) * 4) * BT_M + m;
+            float* dst = prod + (p * 4) * BT_M + m;
             dst[0] = pr.x;
             dst[BT_M] = pr.y;
             dst[2 * BT_M] = pr.z;
             dst[3 * BT_M] = pr.w;
           }
+          named_bar_sync(1, BT_EPI_WARPS * 32);            // every sample's products of this chunk are in shared memory
+          const int nblk = a.ntime / a.ntime_sum, per_tile = a.tile_t / a.ntime_sum, T0 = tt * per_tile;
+          for (int e = threadIdx.x; e < 4 * per_tile * 4; e += BT_EPI_WARPS * 32) {
+            const int comp = e & 3, rest = e >> 2, Tl = rest % per_tile, pair = rest / per_tile;
+            const int pg = (bb * a.nb) / 2 + ch * 4 + pair;
+            if (T0 + Tl >= nblk || 2 * pg + 1 >= a.nbeam) continue;
+            const float* src = prod + (pair * 4 + comp) * BT_M + Tl * a.ntime_sum;
+            float s = 0.f;
+            for (int k = 0; k < a.ntime_sum; ++k) s += src[k];
+            a.pow_out[((static_cast<long>(pg) * nblk + T0 + Tl) * a.nchan + c) * 4 + comp] = s;
+          }
+          named_bar_sync(1, BT_EPI_WARPS * 32);            // sums done before the next chunk's products land
         }
-      }
-      if (FUSED) {
-        named_bar_sync(1, BT_EPI_WARPS * 32);              // every sample's products are in shared memory
-        const int nblk = a.ntime / a.ntime_sum, per_tile = a.tile_t / a.ntime_sum, T0 = tt * per_tile;
-        const int npair = a.nb >> 1;
-        for (int e = threadIdx.x; e < npair * per_tile * 4; e += BT_EPI_WARPS * 32) {
-          const int comp = e & 3, rest = e >> 2, Tl = rest % per_tile, pair = rest / per_tile;
-          const int pg = (bb * a.nb) / 2 + pair;
-          if (T0 + Tl >= nblk || 2 * pg + 1 >= a.nbeam) continue;
-          const float* src = prod + (pair * 4 + comp) * BT_M + Tl * a.ntime_sum;
-          float s = 0.f;
-          for (int k = 0; k < a.ntime_sum; ++k) s += src[k];
-          a.pow_out[((static_cast<long>(pg) * nblk + T0 + Tl) * a.nchan + c) * 4 + comp] = s;
-        }
-        named_bar_sync(1, BT_EPI_WARPS * 32);              // sums done before the next tile's products land
       }
     }
   } else if (warp < BT_WARP_PROD) {
@@ -206,6 +214,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) beamform_tc_kernel(const __grid
     const uint32_t a_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + BT_A_COL0;
     // row m of a 64B-swizzled box: logical 16-byte chunk j sits at chunk j ^ ((m >> 1) & 3)
     const uint32_t row_addr = smem_u32(rawring) + m * BT_KIN, sw = (m >> 1) & 3;
+    const uint32_t scratch = smem_u32(smem) + BT_SCRATCH_OFF + (threadIdx.x - BT_EPI_WARPS * 32) * 4;
     const int nstage_total = ((a.ntiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
                               static_cast<int>(gridDim.x)) * a.nst;      // stages this CTA runs
     for (int gs = g; gs < nstage_total; gs += BT_GROUPS) {
@@ -223,9 +232,10 @@ __global__ void __launch_bounds__(BT_THREADS, 1) beamform_tc_kernel(const __grid
         r[4 * j + 2] = unpack_re4(cur[j].z); r[16 + 4 * j + 2] = unpack_im4(cur[j].z);
         r[4 * j + 3] = unpack_re4(cur[j].w); r[16 + 4 * j + 3] = unpack_im4(cur[j].w);
       }
-      // the unpacked words depend on every byte loaded: once they exist the raw slot may be refilled
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&S->raw_empty[rs]);
+      // The raw slot may be refilled once the loads have RETURNED, not merely issued (an mbarrier arrive does not
+      // wait for outstanding LDS: xeng_corr_tma.cu found that race the hard way): the arrive is ordered behind a
+      // store of a word that depends on every load.
+      mbar_arrive_after(&S->raw_empty[rs], scratch, cur[0].x ^ cur[1].y ^ cur[2].z ^ cur[3].w);
       const int slot = gs % BT_SLOTS;
       mbar_wait(&S->empty[slot], ((gs / BT_SLOTS) & 1) ^ 1, nullptr, 200 + slot);
       tc_fence_after();
@@ -236,40 +246,33 @@ __global__ void __launch_bounds__(BT_THREADS, 1) beamform_tc_kernel(const __grid
       if (lane == 0) mbar_arrive(&S->full[slot]);
     }
   } else if (warp == BT_WARP_PROD) {
-    // ===================================================================== producer (one lane): raw boxes + digit planes
+    // ===================================================================== digit-plane producer (one lane)
     if (lane == 0) {
-      // Two rings of different depth fed by one thread: the raw ring runs ahead of the digit ring, so raw boxes are
-      // issued first for as many stages as their ring has room, then the digit stage that is due.
-      int gs_raw = 0, gs_dig = 0;
-      int tile_raw = blockIdx.x, s_raw = 0, tile_dig = blockIdx.x, s_dig = 0;
-      while (tile_dig < a.ntiles) {
-        // raw boxes: up to BT_RAW_SLOTS - 1 stages ahead of the digit ring, never blocking while a digit stage is due
-        while (tile_raw < a.ntiles && gs_raw < gs_dig + BT_RAW_SLOTS) {
-          const int rs = gs_raw % BT_RAW_SLOTS;
-          if (gs_raw >= BT_RAW_SLOTS && !mbar_try_wait(&S->raw_empty[rs], ((gs_raw / BT_RAW_SLOTS) & 1) ^ 1)) {
-            if (gs_raw > gs_dig) break;                                   // not free yet: go feed the digit ring
-            mbar_wait(&S->raw_empty[rs], ((gs_raw / BT_RAW_SLOTS) & 1) ^ 1, nullptr, 700 + rs);
-          }
-          const int tt = tile_raw % a.ntt, c = (tile_raw / a.ntt) % a.nchan;
-          mbar_arrive_expect_tx(&S->raw_full[rs], BT_RAW_BYTES);
-          tma_load_3d(smem_u32(rawring + rs * BT_RAW_BYTES), &tmap, &S->raw_full[rs], s_raw * BT_KIN, c, tt * a.tile_t);
-          ++gs_raw;
-          if (++s_raw == a.nst) {
-            s_raw = 0;
-            tile_raw += gridDim.x;
-          }
-        }
-        const int cb = tile_dig / a.ntt;                                  // = bb * nchan + c: digit planes are stored [c][bb]
+      int gs = 0;
+      for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
+        const int cb = tile / a.ntt;                       // = bb * nchan + c: digit planes are stored [c][bb]
         const int c = cb % a.nchan, bb = cb / a.nchan;
-        const int8_t* src = a.wdig + ((static_cast<long>(c) * a.nbb + bb) * a.nst + s_dig) * stage_bytes;
-        const int slot = gs_dig % BT_SLOTS;
-        mbar_wait(&S->empty[slot], ((gs_dig / BT_SLOTS) & 1) ^ 1, nullptr, 300 + slot);
-        mbar_arrive_expect_tx(&S->full[slot], stage_bytes);
-        bulk_load(smem_u32(bst + slot * BT_STAGE_MAX), src, stage_bytes, &S->full[slot]);
-        ++gs_dig;
-        if (++s_dig == a.nst) {
-          s_dig = 0;
-          tile_dig += gridDim.x;
+        const int8_t* src = a.wdig + (static_cast<long>(c) * a.nbb + bb) * a.nst * stage_bytes;
+        for (int s = 0; s < a.nst; ++s, ++gs) {
+          const int slot = gs % BT_BSLOTS;
+          mbar_wait(&S->b_empty[slot], ((gs / BT_BSLOTS) & 1) ^ 1, nullptr, 300 + slot);
+          mbar_arrive_expect_tx(&S->b_full[slot], stage_bytes);
+          bulk_load(smem_u32(bst + slot * BT_STAGE_MAX), src + static_cast<long>(s) * stage_bytes, stage_bytes,
+                    &S->b_full[slot]);
+        }
+      }
+    }
+  } else if (warp == BT_WARP_RAW) {
+    // ===================================================================== raw-voltage producer (one lane)
+    if (lane == 0) {
+      int gs = 0;
+      for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
+        const int tt = tile % a.ntt, c = (tile / a.ntt) % a.nchan;
+        for (int s = 0; s < a.nst; ++s, ++gs) {
+          const int rs = gs % BT_RAW_SLOTS;
+          mbar_wait(&S->raw_empty[rs], ((gs / BT_RAW_SLOTS) & 1) ^ 1, nullptr, 700 + rs);
+          mbar_arrive_expect_tx(&S->raw_full[rs], BT_RAW_BYTES);
+          tma_load_3d(smem_u32(rawring + rs * BT_RAW_BYTES), &tmap, &S->raw_full[rs], s * BT_KIN, c, tt * a.tile_t);
         }
       }
     }
@@ -284,15 +287,17 @@ __global__ void __launch_bounds__(BT_THREADS, 1) beamform_tc_kernel(const __grid
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + buf * BT_DCOLS;
         for (int s = 0; s < a.nst; ++s, ++gs) {
-          const int slot = gs % BT_SLOTS;
+          const int slot = gs % BT_SLOTS, bslot = gs % BT_BSLOTS;
+          mbar_wait(&S->b_full[bslot], (gs / BT_BSLOTS) & 1, nullptr, 550 + bslot);
           mbar_wait(&S->full[slot], (gs / BT_SLOTS) & 1, nullptr, 500 + slot);
           tc_fence_after();
-          const uint32_t sb = smem_u32(bst + slot * BT_STAGE_MAX);
+          const uint32_t sb = smem_u32(bst + bslot * BT_STAGE_MAX);
           const uint32_t ta = tmem_base + BT_A_COL0 + slot * BT_ACOLS;
 #pragma unroll
           for (int j = 0; j < 4; ++j)
             umma_i8_ts(tmem_d, ta + j * 8, umma_smem_desc(sb + j * (N * 32), 128, 256), idesc, (s | j) != 0);
           umma_commit(&S->empty[slot]);
+          umma_commit(&S->b_empty[bslot]);
         }
         umma_commit(&S->tmem_full[buf]);
       }
