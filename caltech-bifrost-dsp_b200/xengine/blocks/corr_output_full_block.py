@@ -15,6 +15,7 @@ absent here); the stand-in below writes header + payload to a file object or a U
 simple: transport is outside the X-engine hot path.
 """
 import json
+import os
 import socket
 import struct
 import time
@@ -48,8 +49,11 @@ class CorrOutputFull(Block):
                  dest_port=10000, checkfile=None, checkfile_acc_len=1, antpol_to_bl=None, bl_is_conj=None,
                  use_cor_fmt=True, nchan_sum=1, pipeline_idx=1, npipeline=1, gpu=-1):
         super(CorrOutputFull, self).__init__(log, iring, None, guarantee, core, etcd_client=etcd_client)
-        if checkfile is not None:
-            raise NotImplementedError("checkfile comparison runs in the test-suite against the oracle, not in the block")
+        # expected-output file in make_golden_inputs.py's format: complex128 [time][nchan][nstand][nstand][npol][npol],
+        # each time slice integrated over checkfile_acc_len samples (corr_output_full_block.py:155-166, 395-403)
+        self.checkfile_acc_len = checkfile_acc_len
+        self.checkfile = open(checkfile, 'rb') if checkfile is not None else None
+        self.checkfile_nbytes = os.path.getsize(checkfile) if checkfile is not None else 0
         self.nchan_sum, self.pipeline_idx, self.npipeline = nchan_sum, pipeline_idx, npipeline
         self.nchan, self.npol, self.nstand, self.gpu = nchan, npol, nstand, gpu
         self.words_per_chan = (nstand // 2 + 1) * (nstand // 4) * npol * npol * 4
@@ -108,10 +112,57 @@ class CorrOutputFull(Block):
         rt.stream_synchronize()
         return self.payloads
 
+    # ------------------------------------------------------------------------------------------ checkfile
+    def get_checkfile_corr(self, t):
+        """Integration ``t`` of the check file, wrapping at its end (corr_output_full_block.py:421-437)."""
+        dim = (self.nchan, self.nstand, self.nstand, self.npol, self.npol)
+        nbytes = int(np.prod(dim)) * 16
+        self.checkfile.seek((nbytes * t) % self.checkfile_nbytes)
+        raw = self.checkfile.read(nbytes)
+        if len(raw) != nbytes:
+            self.log.error("CORR OUTPUT >> Failed to get correlation matrix from checkfile")
+            return np.zeros(dim, dtype=complex)
+        return np.frombuffer(raw, dtype=complex).reshape(dim)
+
+    def check_against_file(self, this_gulp_time, upstream_acc_len):
+        """Compare the dump just turned into payloads with the check file, baseline by baseline for s1 >= s0 and
+        every pol product, real and imaginary parts separately -- the reference's in-pipeline check of the conjugation
+        convention (corr_output_full_block.py:550-603), on the per-baseline payloads instead of the square matrix.
+        Returns (good, bad) counts of (baseline, pol product, part) rows; also published as stats."""
+        assert upstream_acc_len % self.checkfile_acc_len == 0, \
+            "CORR OUTPUT >> Testfile acc len not compatible with pipeline acc len"
+        assert this_gulp_time % self.checkfile_acc_len == 0, \
+            "CORR OUTPUT >> Testfile acc len not compatible with pipeline start time"
+        nblocks = upstream_acc_len // self.checkfile_acc_len
+        dtest = np.zeros((self.nchan, self.nstand, self.nstand, self.npol, self.npol), dtype=complex)
+        for i in range(nblocks):
+            dtest += self.get_checkfile_corr(this_gulp_time // self.checkfile_acc_len + i)
+        s0, s1 = np.triu_indices(self.nstand)                       # packet order: s0-major, s1 >= s0
+        want = np.moveaxis(dtest[:, s0, s1], 0, 1)                  # [baseline][chan][p0][p1]
+        got = (self.payloads.numpy() if hasattr(self.payloads, "numpy") else np.asarray(self.payloads))
+        if self.use_cor_fmt:
+            got = got.reshape(self.nbl, self.nchan, self.npol, self.npol, 2)
+        else:                                                        # [baseline][p0][p1][chan][2]
+            got = got.reshape(self.nbl, self.npol, self.npol, self.nchan, 2).transpose(0, 3, 1, 2, 4)
+        ok_re = (got[..., 0] == want.real).all(axis=1)              # [baseline][p0][p1]
+        ok_im = (got[..., 1] == want.imag).all(axis=1)
+        good = int(ok_re.sum() + ok_im.sum())
+        bad = int(ok_re.size + ok_im.size - good)
+        nonzero = int((got[..., 0] != 0).any(axis=1).sum() + (got[..., 1] != 0).any(axis=1).sum())
+        for b in np.argwhere(~(ok_re & ok_im))[:8]:
+            self.log.error("CORR OUTPUT >> test vector mismatch! [%d, %d, %d, %d]" % (s0[b[0]], s1[b[0]], b[1], b[2]))
+        (self.log.error if bad else self.log.info)(
+            "CORR OUTPUT >> test vector check complete. Good: %d, Bad: %d, Non-zero: %d, Zero: %d"
+            % (good, bad, nonzero, ok_re.size + ok_im.size - nonzero))
+        self.update_stats({'checkfile_good': good, 'checkfile_bad': bad})
+        return good, bad
+
     # ------------------------------------------------------------------------------------------ host side
     def _open_destination(self):
         if self.output_file:
             self.output_file.close()
+        if self.checkfile:
+            self.checkfile.close()
             self.output_file = None
         if self.command_vals['dest_file'] != "":
             self.log.info("CORR OUTPUT >> Trying to open file %s for output" % self.command_vals['dest_file'])
@@ -191,6 +242,8 @@ class CorrOutputFull(Block):
                 t = time.time()
                 acquire_time, prev = t - prev, t
                 self.make_payloads(ispan.data)
+                if self.checkfile is not None:
+                    self.check_against_file(this_gulp_time, upstream_acc_len)
                 if self.sink is not None or self.output_file is not None or self.sock is not None:
                     self.send_packets(ihdr, this_gulp_time, upstream_acc_len)
                 t = time.time()
@@ -201,3 +254,5 @@ class CorrOutputFull(Block):
                 this_gulp_time += upstream_acc_len
         if self.output_file:
             self.output_file.close()
+        if self.checkfile:
+            self.checkfile.close()

@@ -308,6 +308,46 @@ def test_corr_output_full_packets(torch_cuda, use_cor_fmt):
                 n += 1
 
 
+@pytest.mark.parametrize("use_cor_fmt", [True, False])
+def test_corr_output_full_checkfile(torch_cuda, tmp_path, use_cor_fmt):
+    """CorrOutputFull(checkfile=...): the reference's in-pipeline check of the whole chain's conjugation convention
+    (corr_output_full_block.py:550-603) against a file in make_golden_inputs.py's format (complex128
+    [time][chan][stand][stand][pol][pol] = sum_t v(s0,p0) conj(v(s1,p1)) per checkfile_acc_len samples): every baseline
+    good on the right file, and a file with one conjugated baseline is caught."""
+    from xengine import ringshim
+    from xengine.blocks import Corr, CorrAcc, CorrOutputFull
+    nstand, npol, nchan, nt, ngulp = 12, 2, 8, 32, 5
+    rng = np.random.default_rng(0xf11e)
+    v = rng.integers(0, 256, size=(ngulp, nt, nchan, nstand, npol), dtype=np.uint8)
+    golden = np.zeros((ngulp, nchan, nstand, nstand, npol, npol), dtype=complex)
+    for g in range(ngulp):
+        fre, fim = orc.corr_full(v[g])
+        golden[g] = fre + 1j * fim
+    good_file, bad_file = tmp_path / "corr_good.dat", tmp_path / "corr_bad.dat"
+    golden.tofile(str(good_file))
+    broken = golden.copy()
+    broken[:, :, 3, 7] = np.conj(broken[:, :, 3, 7])
+    broken.tofile(str(bad_file))
+    for path, expect_bad in ((good_file, 0), (bad_file, None)):
+        r_in = ringshim.Ring("gpu-input", space="cuda")
+        r_corr = ringshim.Ring("corr-output", space="cuda")
+        r_slow = ringshim.Ring("corr-slow-output", space="cuda_host")
+        hdr = header(nchan, nstand, npol)
+        corr = Corr(LOG, r_in, r_corr, ntime_gulp=nt, nchan=nchan, npol=npol, nstand=nstand, acc_len=nt, gpu=0,
+                    autostartat=0, ant_to_input=np.array(hdr['ant_to_input']))
+        acc = CorrAcc(LOG, r_corr, r_slow, nchan=nchan, npol=npol, nstand=nstand, acc_len=2 * nt, gpu=0, autostartat=0)
+        out = CorrOutputFull(LOG, r_slow, nchan=nchan, npol=npol, nstand=nstand, antpol_to_bl=corr.antpol_to_bl,
+                             bl_is_conj=corr.bl_is_conj, use_cor_fmt=use_cor_fmt, gpu=0, checkfile=str(path),
+                             checkfile_acc_len=nt)
+        run_all([source(r_in, hdr, list(v)), threading.Thread(target=corr.main, name="Corr"),
+                 threading.Thread(target=acc.main, name="CorrAcc"), threading.Thread(target=out.main, name="CorrOutputFull")])
+        nrows = nstand * (nstand + 1) // 2 * npol * npol * 2
+        if expect_bad == 0:
+            assert out.stats['checkfile_bad'] == 0 and out.stats['checkfile_good'] == nrows
+        else:       # the imaginary rows of baseline (3, 7), all four pol products
+            assert out.stats['checkfile_bad'] == npol * npol and out.stats['checkfile_good'] == nrows - npol * npol
+
+
 @pytest.mark.parametrize("use_cor_fmt,device_layout", [(False, True), (True, True), (False, False), (True, False)])
 def test_corr_output_part_packets(torch_cuda, use_cor_fmt, device_layout):
     """gpu-input -> Corr -> CorrSubsel -> (cuda_host ring) -> CorrOutputPart, with the payload order produced on the
