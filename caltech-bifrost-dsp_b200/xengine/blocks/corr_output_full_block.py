@@ -161,8 +161,6 @@ class CorrOutputFull(Block):
     def _open_destination(self):
         if self.output_file:
             self.output_file.close()
-        if self.checkfile:
-            self.checkfile.close()
             self.output_file = None
         if self.command_vals['dest_file'] != "":
             self.log.info("CORR OUTPUT >> Trying to open file %s for output" % self.command_vals['dest_file'])
