@@ -50,6 +50,7 @@ class _DevArray(object):
 
     dtype = property(lambda self: self.t.dtype)
     data = property(lambda self: self.t)        # `arr.data[v] = x` (corr_subsel_block.py:249-250)
+    _xeng_raw = property(lambda self: self.t)   # xengine.runtime unwraps foreign arrays through this
 
     def data_ptr(self):
         return self.t.data_ptr() if hasattr(self.t, "data_ptr") else self.t.ctypes.data

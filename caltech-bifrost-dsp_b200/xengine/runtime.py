@@ -11,12 +11,30 @@ import threading
 
 import numpy as np
 
-from .ringshim import WriteSpan, alloc_bytes, np_dtype, view_as  # noqa: F401  (WriteSpan re-exported for blocks)
+from . import ringshim
+from .ringshim import alloc_bytes, np_dtype, view_as  # noqa: F401
 
 try:
     import torch
 except Exception:  # pragma: no cover
     torch = None
+
+
+# ---------------------------------------------------------------------------------------------- rings
+def WriteSpan(ring, size, nonblocking=False):
+    """``bifrost.ring.WriteSpan(oseq.ring, nbytes, nonblocking=False)`` (corr_block.py:435, corr_acc_block.py:312) for
+    whatever kind of ring the block was given: the in-process shim, or any other ring type through the ``bifrost``
+    package that is importable in this process (the real one, or xengine/bfcompat) -- the blocks themselves only use
+    the public ring API listed in SURVEY 8(b)."""
+    if isinstance(ring, ringshim.Ring):
+        return ringshim.WriteSpan(ring, size, nonblocking=nonblocking)
+    import bifrost.ring as _bfring
+    return _bfring.WriteSpan(ring, size, nonblocking=nonblocking)
+
+
+def _unwrap(x):
+    """Arrays of a foreign ring implementation that wrap a torch tensor / numpy array expose it as ``._xeng_raw``."""
+    return getattr(x, "_xeng_raw", x)
 
 
 # ---------------------------------------------------------------------------------------------- devices
@@ -112,15 +130,16 @@ def zeros(shape, dtype, space):
 def copy_array(dst, src):
     """bifrost.ndarray.copy_array(dst, src): any combination of device / pinned / pageable memory, enqueued on
     the current stream (callers follow it with stream_synchronize() before committing a span)."""
+    dst_in, dst, src = dst, _unwrap(dst), _unwrap(src)
     if torch is not None and isinstance(dst, torch.Tensor):
         if not isinstance(src, torch.Tensor):
             src = torch.from_numpy(np.ascontiguousarray(src))
         dst.view(-1).view(torch.uint8).copy_(src.reshape(-1).view(torch.uint8), non_blocking=True)
-        return dst
+        return dst_in
     if torch is not None and isinstance(src, torch.Tensor):
         src = src.detach().cpu().numpy()
     np.copyto(dst.reshape(-1).view(np.uint8), np.ascontiguousarray(src).reshape(-1).view(np.uint8))
-    return dst
+    return dst_in
 
 
 # ---------------------------------------------------------------------------------------------- streams / events

@@ -12,6 +12,7 @@ CALLS = []
 
 def _np(buf):
     """uint8 numpy view of a span buffer (torch CPU tensor or numpy array)."""
+    buf = getattr(buf, "_xeng_raw", buf)       # array of a foreign ring type wrapping a tensor / ndarray
     if hasattr(buf, "numpy"):
         buf = buf.numpy()
     return buf.reshape(-1).view(np.uint8)

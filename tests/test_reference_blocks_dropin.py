@@ -204,6 +204,36 @@ def test_reference_blocks_run_unmodified_over_the_adapter(reference_blocks):
         assert np.allclose(pspans[k].reshape(wantp.shape), wantp, rtol=1e-4, atol=1e-2)
 
 
+def test_our_blocks_run_on_a_foreign_ring_type(host_only, monkeypatch):
+    """INTEGRATION.md option A: THIS repo's blocks on rings that are not the shim -- the ``bifrost.ring.Ring`` of
+    xengine/bfcompat, which exposes only bifrost's public ring API (no shim internals: spans come from
+    ``bifrost.ring.WriteSpan``, span data are foreign array objects).  Host logic only (libxeng doubles)."""
+    for k in [k for k in sys.modules if k.split(".")[0] == "bifrost"]:
+        del sys.modules[k]
+    monkeypatch.syspath_prepend(COMPAT)
+    import bifrost.ring as bfring
+    from xengine.blocks import Corr, CorrAcc
+    r_in, r_corr, r_slow = bfring.Ring(space="cuda"), bfring.Ring(space="cuda"), bfring.Ring(space="cuda_host")
+    for r in (r_in, r_corr, r_slow):
+        assert not hasattr(r, "_commit") and not hasattr(r, "_open_seq")
+    gulps = []
+    for t in range(1, 8):
+        g = np.zeros(NT * NCHAN * NSTAND * NPOL, dtype=np.uint8)
+        g[0] = t
+        gulps.append(g)
+    _fill(r_in, _header(), gulps)
+    corr = Corr(LOG, r_in, r_corr, ntime_gulp=NT, nchan=NCHAN, npol=NPOL, nstand=NSTAND, acc_len=2 * NT, autostartat=0,
+                ant_to_input=np.arange(NINPUT).reshape(NSTAND, NPOL))
+    corr.main()
+    CorrAcc(LOG, r_corr, r_slow, nchan=NCHAN, npol=NPOL, nstand=NSTAND, acc_len=4 * NT, autostartat=0).main()
+    (hdr, spans), = _drain(r_corr, corr.ogulp_size, np.int32)
+    assert hdr['acc_len'] == 2 * NT and [tuple(s[:2]) for s in spans] == [(1 + 2, 2), (3 + 4, 2), (5 + 6, 2)]
+    (shdr, sspans), = _drain(r_slow, corr.ogulp_size, np.int32)
+    assert shdr['upstream_acc_len'] == 2 * NT and [int(s[0]) for s in sspans] == [1 + 2 + 3 + 4]
+    for k in [k for k in sys.modules if k.split(".")[0] == "bifrost"]:
+        del sys.modules[k]
+
+
 @pytest.mark.gpu
 def test_adapter_call_sequence_on_the_gpu():
     """The reference blocks' ``_bf.*`` call sequence on the real library (device memory, compat arrays)."""
