@@ -464,6 +464,10 @@ def run_b200(args):
     fast = [torch.zeros((nchan // NSUM, NVIS, 2), dtype=torch.int32, device=dev) for _ in range(2)]
 
     def barrier():
+        # synchronize on BOTH sides of the rendezvous: a rank's side-stream traffic (a 766 MB dump still streaming
+        # into rank 0) must have landed before any rank starts the next timed region, or the early ranks' first
+        # pushes queue behind it (r02o: one 0.6 ms step on every non-root rank)
+        torch.cuda.synchronize(dev)
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
@@ -604,6 +608,30 @@ def run_b200(args):
         dmp1.record(stream)
     barrier()
     dump_ms = dmp0.elapsed_time(dmp1)
+    # what a dump costs when it travels beside the correlator, as it does at its true cadence: M steps with one dump
+    # launched on the side stream at their start, against the same M steps alone (M steps outlast the dump)
+    M = max(8, int(1.5 * dump_ms / max(kern_ms, 1e-3)) + 4)
+
+    def m_steps(with_dump):
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            launch_step(d_in[0], 0, True)                      # untimed; its result seeds the dump
+            a0.record(stream)
+            if with_dump:
+                dump_device()
+            for j in range(M):
+                launch_step(d_in[j % NBUF], j % NBUF, False)
+            if world > 1:
+                stream.wait_stream(gstream)
+                stream.wait_stream(pstream)
+            a1.record(stream)
+        barrier()
+        return a0.elapsed_time(a1)
+
+    t_plain = m_steps(False)
+    t_dump = m_steps(True)
+    dump_overlapped_ms = max(0.0, t_dump - t_plain)
     gather_ok = push_ok = None
     if world > 1:                                           # what arrived on rank 0 is what each rank sent
         with torch.cuda.stream(pstream):
@@ -703,21 +731,25 @@ def run_b200(args):
                             vm, cj, stream, h_in, barrier)
 
     # ---- max over ranks (+ every rank's own per-step figures on rank 0)
-    amort_ms = 0.0 if ndump > 0 else dump_ms * K / accg      # no long dump fell in the timed region: charge its share
+    amort_ms = 0.0 if ndump > 0 else dump_overlapped_ms * K / accg   # no long dump fell in the timed region: charge its share
     per_rank = None
     if world > 1:
-        t = torch.tensor([total_ms, e2e_ms, kern_ms, dump_ms, h2d_probe_gbs], dtype=torch.float64, device=dev)
+        t = torch.tensor([total_ms, e2e_ms, kern_ms, dump_ms, h2d_probe_gbs, dump_overlapped_ms], dtype=torch.float64,
+                         device=dev)
         allt = [torch.empty_like(t) for _ in range(world)]
         dist.all_gather(allt, t)
         sv = torch.tensor(step_ms, dtype=torch.float64, device=dev)
         allsv = [torch.empty_like(sv) for _ in range(world)]
         dist.all_gather(allsv, sv)
         per_rank = [{"rank": r, "total_ms": float(allt[r][0]), "e2e_ms": float(allt[r][1]),
-                     "step_ms": stats(allsv[r].cpu().numpy()), "h2d_probe_gbs": float(allt[r][4]),
+                     "step_ms": stats(allsv[r].cpu().numpy()),
+                     "steps_ms": [round(float(x), 4) for x in allsv[r].cpu().numpy()],
+                     "h2d_probe_gbs": float(allt[r][4]),
                      "e2e_h2d_gbs": in_bytes * K / float(allt[r][1]) / 1e6} for r in range(world)]
         m = torch.stack(allt).max(dim=0).values
         total_ms, e2e_ms, kern_ms, dump_ms = [float(x) for x in m[:4].tolist()]
-        amort_ms = 0.0 if ndump > 0 else dump_ms * K / accg
+        dump_overlapped_ms = float(m[5])
+        amort_ms = 0.0 if ndump > 0 else dump_overlapped_ms * K / accg
 
     if rank == 0:
         hbm_peak, peak_src = peaks()
@@ -770,15 +802,18 @@ def run_b200(args):
             "gpu_launches": K,
             "gpu_launches_whole_run": nlaunch[0],
             "step_ms": stats(step_ms),
-            "dump": {"in_timed_region": ndump, "every_steps": accg, "alone_ms": dump_ms, "gather_verified": gather_ok,
+            "dump": {"in_timed_region": ndump, "every_steps": accg, "alone_ms": dump_ms,
+                     "overlapped_cost_ms": dump_overlapped_ms, "gather_verified": gather_ok,
                      "amortised_ms_added_per_step": amort_ms / K,
                      "gather": None if world == 1 else ("NCCL dist.gather" if args.nccl_gather else
                                                         "peer writes into rank 0's symmetric-memory buffer (copy engines over NVLink)"),
                      "bytes_to_rank0": (world - 1) * out_words * 4,
                      "note": "dumps fall at their true cadence (every acc_gulps steps); alone_ms is one dump "
-                             "(device copy + gather to rank 0) timed with nothing to overlap; when no dump falls "
-                             "inside the timed region its share alone_ms * steps / acc_gulps is ADDED to the timed "
-                             "total (no overlap assumed) before value and ms_per_step are formed"},
+                             "(device copy + gather to rank 0) timed with nothing to overlap; overlapped_cost_ms is "
+                             "what a dump adds to a run of steps it travels beside (side stream, copy engines), "
+                             "measured as (M steps + 1 dump) - (M steps), max over ranks; when no dump falls inside "
+                             "the timed region its share overlapped_cost_ms * steps / acc_gulps is ADDED to the "
+                             "timed total before value and ms_per_step are formed"},
             "roofline": {"kernel": "corr_swz_kernel (fused Corr+CorrAcc%s)" % ("+CorrSubsel" if fused_fast else ""),
                          "bound": "hbm", "achieved": achieved,
                          "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
