@@ -637,7 +637,7 @@ def run_b200(args):
         with torch.cuda.stream(pstream):
             fpush.finish()
         torch.cuda.synchronize(dev)
-        last = last_seq
+        last = seqc[0] - 1                                   # the most recent step of all (the dump-overlap runs above)
         probe = torch.stack([d_dump[:4096].to(torch.int64).sum(), d_dump[-4096:].to(torch.int64).sum(),
                              fast[last % 2].to(torch.int64).sum(), fast[last % 2][-1].to(torch.int64).sum()])
         sent = [torch.empty_like(probe) for _ in range(world)]
