@@ -375,6 +375,20 @@ def path_kernels(torch, ops, dev, nchan, hbm_peak, iters=10):
     ms_f = timeit(lambda: bf.run_integrate(vv, po, w, nsum))
     res["beamform_power_fused"] = {"ms": ms_f, "gsamples_per_s": nt * nchan * NINPUT / ms_f / 1e6,
                                    "tflops_fp32": fl / ms_f / 1e9, "unfused_ms": res["beamform"]["ms"] + ms}
+    res["beamform"]["note"] = "tcgen05 int8 digit-plane kernel, weights converted on EVERY call (bfBeamformRun's convention)"
+    bf.set_weights(w)            # converted once, as the Beamform block does at each coefficient update
+    ms_p = timeit(lambda: bf.run(vv, bo, None))
+    ms_pf = timeit(lambda: bf.run_integrate(vv, po, None, nsum))
+    ms_c = timeit(lambda: bf.set_weights(w))
+    alg = vv.numel() + bo.numel() * 4 + 6 * nbeam * 2 * NINPUT * nchan
+    res["beamform_weights_preloaded"] = {"ms": ms_p, "gsamples_per_s": nt * nchan * NINPUT / ms_p / 1e6,
+                                         "fp32_equiv_tflops": fl / ms_p / 1e9, "int8_tops": 3 * fl / ms_p / 1e9,
+                                         "alg_bytes": alg, "gbs": alg / ms_p / 1e6, "frac_hbm": alg / ms_p / 1e6 / hbm_peak,
+                                         "power_fused_ms": ms_pf, "weight_conversion_ms": ms_c}
+    bf.set_impl(1)
+    ms_32 = timeit(lambda: bf.run(vv, bo, w), 4)
+    res["beamform_fp32_kernel"] = {"ms": ms_32, "tflops_fp32": fl / ms_32 / 1e9,
+                                   "note": "the CUDA-core cross-check implementation (r1's kernel)"}
     bf.close()
     del vv, w, bo, po
     # offline upchannelise path at the scripts' sizes: 480-sample gulp = 15 frames x 32 fine samples,

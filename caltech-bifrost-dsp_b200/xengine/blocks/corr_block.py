@@ -10,8 +10,11 @@ Differences that do not change the data products:
     is no library-internal accumulator to go stale when an input sequence ends mid-integration;
   * ``acc_len = 0`` stops cleanly (the reference falls through to ``WriteSpan(None.ring, ...)``,
     corr_block.py:421-435);
-  * ``test=True`` cross-checks every dump on the GPU against the independent CUDA-core kernel instead of running
-    numpy for ~10 minutes per gulp (corr_block.py:265-315).
+  * ``test=True`` cross-checks every dump on the GPU against this library's second, CUDA-core implementation. That is
+    a fast on-line consistency check between two kernels by the same author; it is NOT the equivalent of the
+    reference's in-line numpy ``_test`` / ``_compare`` (corr_block.py:265-315, ~10 minutes per gulp), whose role --
+    parity with the reference's formulation -- is played by the oracle in ``tests/`` (restated as
+    ``oracle.corr_loop_literal`` and pinned to the reference's own ``Corr._test`` output).
 
 Optional keyword arguments at the END of the signature (all default to the reference's behaviour):
 
