@@ -20,7 +20,7 @@
 //            K = 2 ninput stacked [re | im], N = 3 digits x 2 (re, im) x nb beams (192 for 32 beams), B rows
 //                out_re(b): [ w_re | -w_im ]      out_im(b): [ w_im | w_re ]
 //   A        lives in TENSOR MEMORY (tcgen05.mma with the A operand in TMEM, K-major).  The producer warp brings RAW
-//            4+4-bit boxes {64 inputs, 1 channel, 128 samples} into an 8-deep shared-memory ring with TMA
+//            4+4-bit boxes {64 inputs, 1 channel, 128 samples} into a 6-deep shared-memory ring with TMA
 //            (SWIZZLE_64B; a thread reading its own sample's 64 bytes straight from global memory costs a warp 32
 //            sector requests per 16-byte load -- the first version of this kernel was L1-request bound on exactly
 //            that); an unpack thread takes its sample's row with four conflict-free LDS.128, sign-extends the
@@ -28,7 +28,8 @@
 //            never touch shared memory.
 //   B        digit planes are precomputed in global memory in exactly the K-major no-swizzle core-matrix layout the
 //            MMA reads ([n/8][k/16][n%8][16 B] per 32-deep K-block), so one stage (64 inputs = 4 MMAs) is ONE 1-D
-//            bulk copy (cp.async.bulk, 24 KB) into a 4-deep shared-memory ring.
+//            bulk copy (cp.async.bulk, 24 KB) into a 6-deep shared-memory ring of its own (an L2 -> SM copy needs
+//            ~1300 cycles to land; sharing the A slots' depth of 4 left the MMA warp waiting for digits).
 //   D        two accumulators of N columns (double buffered): the epilogue of tile i overlaps the MMAs of tile i+1.
 //   epilogue 4 warps (one per TMEM lane quarter; lane = time sample): tcgen05.ld the three digit sums of 8 beams,
 //            recombine in fp32, scale, and either store cf32 voltages [c][b][t] (a warp writes 256 contiguous bytes
@@ -36,8 +37,8 @@
 //            ntime_sum samples in time order (beamform_sum_beams_block.py:245; beamformer_sum_test.py:64-77) --
 //            the same expressions and order as beam_integrate_kernel, so both paths agree bit for bit.
 //
-// Roles (576 threads): warps 0-3 epilogue, 4-15 unpack (3 groups x 4 lane quarters, a group per stage), 16 producer
-// (raw TMA boxes + digit-plane bulk copies), 17 MMA issuer.  Persistent grid, one CTA per SM,
+// Roles (608 threads): warps 0-3 epilogue, 4-15 unpack (3 groups x 4 lane quarters, a group per stage; A slots in TMEM
+// columns 384..511, 4 deep), 16 digit-plane producer, 17 raw-voltage producer, 18 MMA issuer.  Persistent grid, one CTA per SM,
 // tiles ordered (beam block, channel, time tile) so the CTAs working at one moment share a channel's digits in L2.
 #include <cuda.h>
 
