@@ -625,6 +625,10 @@ def run_b200(args):
     # what a dump costs when it travels beside the correlator, as it does at its true cadence: M steps with one dump
     # launched on the side stream at their start, against the same M steps alone (M steps outlast the dump)
     M = max(8, int(1.5 * dump_ms / max(kern_ms, 1e-3)) + 4)
+    if world > 1:                                              # the same number of steps (and pushes) on every rank
+        mt = torch.tensor([M], device=dev)
+        dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+        M = int(mt)
 
     def m_steps(with_dump):
         barrier()
