@@ -51,6 +51,8 @@ def parse():
     p.add_argument("--acc-gulps", type=int, default=250)
     p.add_argument("--nccl-gather", action="store_true",
                    help="gather dumps with dist.gather (NCCL kernels) instead of copy-engine peer writes")
+    p.add_argument("--push", default="sm", choices=["sm", "ce"],
+                   help="per-step products to rank 0: xeng_peer_push (SM stores) or cudaMemcpyAsync (copy engines)")
     p.add_argument("--cpu-seconds", type=float, default=15.0, help="budget for the cpu_baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-path-kernels", action="store_true", help="skip the per-kernel figures of the rest of the path")
@@ -495,7 +497,7 @@ def run_b200(args):
         if not args.nccl_gather:
             try:
                 peer = sharding.PeerGather(out_words, torch.int32, dev, dist, root=0)
-                fpush = sharding.PeerStream(fast[0].numel(), torch.int32, dev, dist, nslot=2, root=0)
+                fpush = sharding.PeerStream(fast[0].numel(), torch.int32, dev, dist, nslot=2, root=0, via=args.push)
             except Exception as e:                              # no symmetric memory on this node: all ranks use NCCL
                 sys.stderr.write("rank %d: symmetric-memory peer writes unavailable (%s)\n" % (rank, e))
                 peer = fpush = None
@@ -507,7 +509,9 @@ def run_b200(args):
             push_kind = "NCCL dist.gather every step"
         else:
             d_dump = peer.slot if rank == 0 else d_dump    # rank 0 snapshots straight into its own slot
-            push_kind = "peer writes into rank 0's symmetric-memory slots (copy engines over NVLink), no cross-rank wait"
+            push_kind = ("peer writes into rank 0's symmetric-memory slots over NVLink (%s), no cross-rank wait"
+                         % ("xeng_peer_push: SM stores from CTAs resident beside the correlator" if args.push == "sm"
+                            else "cudaMemcpyAsync: copy engines"))
     if world > 1 and rank == 0 and args.nccl_gather:
         gather_list = [d_dump] + [torch.empty_like(d_dump) for _ in range(world - 1)]
 
@@ -526,6 +530,7 @@ def run_b200(args):
                 else:
                     sharding.gather_to_root(d_dump, dist, root=0, out=gather_list)
 
+    push_launches = 2 if getattr(fpush, "via", None) == "sm" else 0
     fast_done = [torch.cuda.Event() for _ in range(2)]
     fast_free = [torch.cuda.Event() for _ in range(2)]
     counts = [0] * NBUF                                      # gulps of each buffer in the running integration
@@ -553,6 +558,7 @@ def run_b200(args):
         with torch.cuda.stream(pstream):
             pstream.wait_event(fast_done[slot])
             fpush.push(fast[slot], seq)
+            nlaunch[0] += push_launches                      # xeng_peer_push: payload kernel + sequence-word kernel
             fast_free[slot].record(pstream)
         return seq
 
@@ -817,7 +823,7 @@ def run_b200(args):
                     "h2d_probe_gbs": h2d_probe_gbs,
                     "note": "h2d_probe_gbs = plain pinned cudaMemcpyAsync of the same gulp with nothing else running "
                             "(the PCIe ceiling of this box); the e2e rate is input bytes / time, 1 B per sample"},
-            "gpu_launches": K,
+            "gpu_launches": K * (1 + push_launches),
             "gpu_launches_whole_run": nlaunch[0],
             "step_ms": stats(step_ms),
             "dump": {"in_timed_region": ndump, "every_steps": accg, "alone_ms": dump_ms,
@@ -894,8 +900,8 @@ def xengine_full(torch, dist, ops, sharding, orc, args, dev, world, rank, xc, d_
     pstream = torch.cuda.Stream(device=dev)
     if world > 1:
         try:
-            fpush = sharding.PeerStream(fast[0].numel(), torch.int32, dev, dist, nslot=2, root=0)
-            ppush = sharding.PeerStream(pw[0].numel(), torch.float32, dev, dist, nslot=2, root=0)
+            fpush = sharding.PeerStream(fast[0].numel(), torch.int32, dev, dist, nslot=2, root=0, via=args.push)
+            ppush = sharding.PeerStream(pw[0].numel(), torch.float32, dev, dist, nslot=2, root=0, via=args.push)
             ok = 1
         except Exception:
             ok = 0
@@ -924,9 +930,11 @@ def xengine_full(torch, dist, ops, sharding, orc, args, dev, world, rank, xc, d_
             pstream.wait_event(a_done[s])
             if fpush is not None:
                 fpush.push(fast[s], seq)
+                nlaunch[0] += 2 if getattr(fpush, "via", None) == "sm" else 0
             pstream.wait_event(b_done[s])
             if ppush is not None:
                 ppush.push(pw[s], seq)
+                nlaunch[0] += 2 if getattr(ppush, "via", None) == "sm" else 0
             slot_free[s].record(pstream)
 
     def run(n, srcs, e2e, reset):

@@ -490,6 +490,31 @@ int xeng_upchan_beamform(const void* d_in, const void* d_weights, void* d_out, i
   return XENG_OK;
 }
 
+int xeng_memcpy_async(void* dst, const void* src, size_t nbytes, void* stream) {
+  if (!dst || !src) return fail(XENG_ERR_ARG, "null pointer");
+  if (nbytes == 0) return XENG_OK;
+  XENG_CUDA(cudaMemcpyAsync(dst, src, nbytes, cudaMemcpyDefault, static_cast<cudaStream_t>(stream)));
+  return XENG_OK;
+}
+
+int xeng_peer_push(void* dst, const void* src, size_t nbytes, void* dst_seq, long long seq, void* stream) {
+  if (!dst || !src) return fail(XENG_ERR_ARG, "null pointer");
+  if ((nbytes & 15) || (reinterpret_cast<uintptr_t>(dst) & 15) || (reinterpret_cast<uintptr_t>(src) & 15))
+    return fail(XENG_ERR_ARG, "xeng_peer_push wants 16-byte aligned pointers and a multiple of 16 bytes");
+  if (dst_seq && (reinterpret_cast<uintptr_t>(dst_seq) & 7)) return fail(XENG_ERR_ARG, "dst_seq must be 8-byte aligned");
+  static int nsm_of[64] = {0};
+  int dev = 0;
+  XENG_CUDA(cudaGetDevice(&dev));
+  int nsm = (dev >= 0 && dev < 64) ? nsm_of[dev] : 0;
+  if (!nsm) {
+    XENG_CUDA(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
+    if (dev >= 0 && dev < 64) nsm_of[dev] = nsm;
+  }
+  XENG_CUDA(xeng::launch_peer_push(dst, src, nbytes, static_cast<long long*>(dst_seq), seq, nsm,
+                                   static_cast<cudaStream_t>(stream)));
+  return XENG_OK;
+}
+
 // ------------------------------------------------------------------------------------ Beamform
 int xeng_bf_create(xeng_bf_t* out, int gpu, int ninput, int nchan, int ntime, int nbeam, int ntime_blocks) {
   if (!out) return fail(XENG_ERR_ARG, "null handle pointer");

@@ -151,6 +151,19 @@ def reorder_packets(d_in, d_out, d_a2bl, d_conj, nstand, npol, nchan, wpc, layou
                                            layout, ptr(stream)), "xeng_reorder_packets")
 
 
+def memcpy_async(dst, src, nbytes, stream=None):
+    """cudaMemcpyAsync(cudaMemcpyDefault) on `stream`: a copy-engine copy between any two unified addresses (device,
+    pinned host, peer memory mapped into this process)."""
+    check(_lib.load().xeng_memcpy_async(ptr(dst), ptr(src), int(nbytes), ptr(stream)), "xeng_memcpy_async")
+
+
+def peer_push(dst, src, nbytes, dst_seq=None, seq=0, stream=None):
+    """`nbytes` from src to dst by SM stores, then (dst_seq given) the 64-bit word `seq` to dst_seq, released after the
+    payload.  dst / dst_seq may be peer memory mapped into this process.  See include/xeng.h (xeng_peer_push)."""
+    check(_lib.load().xeng_peer_push(ptr(dst), ptr(src), int(nbytes), ptr(dst_seq), int(seq), ptr(stream)),
+          "xeng_peer_push")
+
+
 class Beamformer(object):
     """bfBeamformInitialize / Run / Integrate / IntegrateSingleBeam
     (beamform_block.py:251,449; beamform_sum_beams_block.py:245; beamform_sum_single_beam_block.py:114)."""

@@ -36,6 +36,16 @@ def slab_of(array, rank, world_size, axis=0):
     return array[tuple(index)]
 
 
+def _ce_copy(dst, src):
+    """dst <- src on the current torch stream through the COPY ENGINES (xeng_memcpy_async).  A tensor.copy_() onto a
+    peer buffer that symmetric memory mapped into this process is, to torch, a same-device copy: an SM kernel, which
+    has to share the SMs with the persistent correlator (r02t: a 766 MB dump cost 6.4 of its 7.0 ms even 'overlapped')."""
+    import torch
+    from . import ops
+    assert dst.is_contiguous() and src.is_contiguous() and dst.numel() * dst.element_size() == src.numel() * src.element_size()
+    ops.memcpy_async(dst, src, dst.numel() * dst.element_size(), torch.cuda.current_stream(dst.device))
+
+
 def gather_to_root(tensor, dist, root=0, out=None):
     """Gather every rank's product (same shape on all ranks) to ``root``; returns the list ordered by rank (i.e. by
     channel slab) on root, None elsewhere.  ``dist`` is torch.distributed (NCCL over NVLink on GPUs, gloo in the
@@ -79,7 +89,7 @@ class PeerGather(object):
             flat = src.reshape(-1)
             step = max(1, self.chunk_bytes // flat.element_size())
             for i in range(0, flat.numel(), step):
-                self.slot[i:i + step].copy_(flat[i:i + step], non_blocking=True)
+                _ce_copy(self.slot[i:i + step], flat[i:i + step])
         self.hdl.barrier(channel=0)
 
     def parts(self):
@@ -94,15 +104,23 @@ class PeerStream(object):
     and BeamformSum's powers every gulp (beamform_sum_beams_block.py:245-247), which the reference sends as UDP
     packets to a central receiver -- as a stream of peer writes to ``root``: ``root`` owns ``nslot`` x [world][n]
     slots in torch symmetric memory plus one sequence word per (slot, rank); ``push(src, seq)`` stores this rank's
-    product of step ``seq`` into slot ``seq % nslot`` with one device-to-device copy and then its sequence number
-    with a second, both on the current stream (copy engines over NVLink, in order; no SMs, no cross-rank wait: the
-    producer never blocks on the consumer).  A consumer on root that sees ``seq`` in the word knows the payload
-    before it has landed.  ``finish()`` is the one barrier, at the end of a run."""
+    product of step ``seq`` into slot ``seq % nslot`` and then its sequence number, both on the current stream, with
+    no cross-rank wait: the producer never blocks on the consumer.  A consumer on root that sees ``seq`` in the word
+    knows the payload has landed.  ``finish()`` is the one barrier, at the end of a run.
 
-    def __init__(self, n, dtype, device, dist, nslot=2, root=0, max_seq=1 << 16):
+    ``via="sm"`` (default) sends with xeng_peer_push: 128-thread CTAs that fit on an SM beside the persistent
+    correlator and store straight into the peer mapping.  ``via="ce"`` sends with two cudaMemcpyAsync copies; those
+    share the copy-engine queue with the long dump (PeerGather) and wait behind it (profiles/r02v_bench_n2.json)."""
+
+    def __init__(self, n, dtype, device, dist, nslot=2, root=0, max_seq=1 << 16, via="sm"):
         import torch
         import torch.distributed._symmetric_memory as symm_mem
-        self.dist, self.root, self.n, self.nslot = dist, root, n, nslot
+        if via not in ("sm", "ce"):
+            raise ValueError("via must be 'sm' or 'ce'")
+        self.dist, self.root, self.n, self.nslot, self.via = dist, root, n, nslot, via
+        self.nbytes = n * torch.empty((), dtype=dtype).element_size()
+        if via == "sm" and self.nbytes % 16:
+            raise ValueError("PeerStream(via='sm') wants a product that is a multiple of 16 bytes")
         self.rank, self.world = dist.get_rank(), dist.get_world_size()
         self.buf = symm_mem.empty(nslot * self.world * n, dtype=dtype, device=device)
         self.seqbuf = symm_mem.empty(nslot * self.world, dtype=torch.int64, device=device)
@@ -115,8 +133,16 @@ class PeerStream(object):
 
     def push(self, src, seq):
         slot = seq % self.nslot
-        self.root_buf[slot, self.rank].copy_(src.reshape(-1), non_blocking=True)
-        self.root_seq[slot, self.rank].copy_(self.numbers[seq % self.numbers.numel()], non_blocking=True)
+        if self.via == "sm":
+            import torch
+            from . import ops
+            src = src.reshape(-1)
+            assert src.is_contiguous() and src.numel() == self.n
+            ops.peer_push(self.root_buf[slot, self.rank], src, self.nbytes, self.root_seq[slot, self.rank], seq,
+                          torch.cuda.current_stream(src.device))
+            return
+        _ce_copy(self.root_buf[slot, self.rank], src.reshape(-1))
+        _ce_copy(self.root_seq[slot, self.rank], self.numbers[seq % self.numbers.numel()])
 
     def finish(self):
         self.hdl.barrier(channel=0)

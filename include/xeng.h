@@ -144,6 +144,21 @@ int xeng_upchan_fft(const void* d_in, void* d_out, int nframe, int nfine, int nc
 int xeng_upchan_beamform(const void* d_in, const void* d_weights, void* d_out, int nframe, int nfine, int nchan,
                          int ninput, int nbeam, void* cuda_stream);
 
+/* Plain asynchronous copy between any two addresses of the unified address space (device, pinned host, a peer
+ * GPU's memory mapped into this process) on `cuda_stream`: cudaMemcpyAsync(cudaMemcpyDefault), i.e. the COPY ENGINES.
+ * The gathers of finished products to rank 0 (xengine/sharding.py; the reference sends them as UDP packets,
+ * corr_subsel_block.py:298-305, corr_acc_block.py:312-317) use it because a framework-level tensor copy onto a
+ * peer-mapped buffer is an SM kernel, which would have to share the SMs with the persistent correlator. */
+int xeng_memcpy_async(void* dst, const void* src, size_t nbytes, void* cuda_stream);
+
+/* One per-step product to its receiver by SM stores: `nbytes` (a multiple of 16; both pointers 16-byte aligned) from
+ * `src` to `dst`, then -- when dst_seq is not NULL -- the 64-bit word `seq` to `dst_seq`, released at system scope
+ * after the payload.  dst / dst_seq may be a peer GPU's memory mapped into this process (torch symmetric memory):
+ * this is the path's replacement for the reference's per-integration UDP sends of CorrSubsel's fast dump
+ * (corr_subsel_block.py:298-305) and BeamformSum's powers (beamform_sum_beams_block.py:245-247).  Small CTAs that fit
+ * beside the persistent correlator; nothing on the copy-engine queue the long dump occupies. */
+int xeng_peer_push(void* dst, const void* src, size_t nbytes, void* dst_seq, long long seq, void* cuda_stream);
+
 /* ------------------------------------------------------------------ Beamform / BeamformSum */
 typedef struct xeng_bf_s* xeng_bf_t;
 

@@ -41,3 +41,38 @@ def test_handles_on_two_devices_in_one_process():
             g = volt.cpu().numpy()
             assert np.abs(g[..., 0] + 1j * g[..., 1] - wantv).max() / np.abs(wantv).max() <= 1e-5, (dev, impl)
         bf.close()
+
+
+@pytest.mark.gpu
+def test_peer_push_payload_then_sequence_word():
+    """xeng_peer_push: the payload lands, then the sequence word; misaligned calls are refused."""
+    import torch
+    from xengine import ops
+    from xengine._lib import XengError
+    dev = torch.device("cuda:0")
+    n = 4704 * 48 * 2 + 4                                     # a fast dump's words, plus a ragged tail of one int4
+    src = torch.randint(-2 ** 31, 2 ** 31 - 1, (n,), dtype=torch.int32, device=dev)
+    dst = torch.zeros(n + 8, dtype=torch.int32, device=dev)
+    flag = torch.full((2,), -1, dtype=torch.int64, device=dev)
+    stream = torch.cuda.Stream(device=dev)
+    with torch.cuda.stream(stream):
+        ops.peer_push(dst[4:], src, n * 4, flag[1:], 77, stream)
+    stream.synchronize()
+    assert torch.equal(dst[4:4 + n], src) and int(dst[:4].abs().sum()) == 0 and int(dst[4 + n:].abs().sum()) == 0
+    assert flag.tolist() == [-1, 77]
+    ops.peer_push(dst, src, 0, flag, 5, stream)             # empty payload: only the word moves
+    stream.synchronize()
+    assert flag.tolist() == [5, 77]
+    if torch.cuda.device_count() > 1 and torch.cuda.can_device_access_peer(0, 1):
+        far = torch.zeros(n, dtype=torch.int32, device="cuda:1")
+        far.copy_(src)                                        # torch enables peer access on its first peer copy
+        far.zero_()
+        torch.cuda.synchronize("cuda:1")
+        with torch.cuda.device(dev):
+            ops.peer_push(far, src, n * 4, None, 0, stream)
+            stream.synchronize()
+        assert torch.equal(far.to(dev), src)
+    for bad in (lambda: ops.peer_push(dst[1:], src, 16, None, 0, stream),
+                lambda: ops.peer_push(dst, src, 20, None, 0, stream)):
+        with pytest.raises(XengError):
+            bad()
