@@ -670,6 +670,23 @@ int xeng_bf_integrate_single(xeng_bf_t h, const void* d_in, void* d_out, int nti
   return XENG_OK;
 }
 
+int xeng_beam_power_static(const void* d_in, const void* d_w, void* d_out, int ninput, int nchan, int ntime, int nbeam,
+                           int ntime_sum, void* stream) {
+  if (!d_in || !d_w || !d_out) return fail(XENG_ERR_ARG, "null pointer");
+  if (ninput <= 0 || nchan <= 0 || ntime <= 0 || nbeam <= 0) return fail(XENG_ERR_ARG, "sizes must be positive");
+  if (ntime_sum <= 0 || (nbeam & 1) || ntime % ntime_sum)
+    return fail(XENG_ERR_ARG, "need ntime_sum | ntime and an even number of beams");
+  const unsigned long long nvolt = 1ull * nchan * nbeam * static_cast<unsigned long long>(ntime);
+  if (nvolt > xeng::beam_power_static_capacity())
+    return fail(XENG_ERR_ARG, "xeng_beam_power_static: nchan*nbeam*ntime = %llu beam voltages exceed the static scratch "
+                "array (XENG_STATIC_SCRATCH_FLOAT2 = %llu); use xeng_bf_run_integrate", nvolt,
+                static_cast<unsigned long long>(xeng::beam_power_static_capacity()));
+  XENG_CUDA(xeng::launch_beam_power_static(static_cast<const uint8_t*>(d_in), static_cast<const float2*>(d_w),
+                                           static_cast<float*>(d_out), ninput, nchan, ntime, nbeam, ntime_sum,
+                                           static_cast<cudaStream_t>(stream)));
+  return XENG_OK;
+}
+
 int xeng_bf_sync(xeng_bf_t h) {
   if (!h) return fail(XENG_ERR_ARG, "null handle");
   cudaError_t e = cudaStreamSynchronize(h->stream);

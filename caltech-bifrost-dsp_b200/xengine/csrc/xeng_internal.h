@@ -106,6 +106,10 @@ bool beam_tc_supported(const BeamArgs& a);
 cudaError_t launch_beam_weight_digits(const float2* w, int8_t* dig, float* scale, int nchan, int nbeam, int ninput,
                                       cudaStream_t stream);
 cudaError_t launch_beamform_tc(const BeamArgs& a, const int8_t* dig, const float* scale, int nsm, cudaStream_t stream);
+// no-allocation Beamform + BeamformSum (xeng_static.cu): beam voltages in a static __device__ array
+size_t beam_power_static_capacity();
+cudaError_t launch_beam_power_static(const uint8_t* in, const float2* w, float* pow_out, int ninput, int nchan,
+                                     int ntime, int nbeam, int ntime_sum, cudaStream_t stream);
 #ifdef __CUDACC__
 // [|X|^2, |Y|^2, Re X Y*, Im X Y*] of one sample (beamformer_sum_test.py:64-77).  Explicit fma/mul so that every
 // kernel forming these products (stand-alone integrate, both fused beamformer epilogues) rounds identically.

@@ -191,6 +191,21 @@ int xeng_bf_integrate_single(xeng_bf_t h, const void* d_in, void* d_out, int nti
  * HBM.  With the tap on (or a longer ntime_sum) it is the beamformer followed by the integration kernel, the voltage
  * beams staying in a handle-owned scratch buffer readable through xeng_bf_voltages (a VLBI-style tap). */
 int xeng_bf_run_integrate(xeng_bf_t h, const void* d_in, void* d_out, const void* d_weights, int ntime_sum);
+
+/* No counterpart in the reference: added for callers that cannot allocate
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Beamform followed by
+ * BeamformSum on the CURRENT device, no handle: d_in 4+4-bit [ntime][nchan][ninput], d_weights cf32
+ * [nchan][nbeam][ninput], d_out f32 [nbeam/2][ntime/ntime_sum][nchan][4] -- the result of xeng_bf_run_integrate with the
+ * fp32 kernel.  The intermediate beam voltages live in a `static __device__` array inside the library
+ * (XENG_STATIC_SCRATCH_BYTES on every GPU that loads libxeng, until the process exits); the call makes no cudaMalloc /
+ * cudaFree and returns XENG_ERR_ARG when nchan*nbeam*ntime > XENG_STATIC_SCRATCH_FLOAT2.  Every call on a device
+ * shares that array and finds the previous call's voltages in it (nothing needs to start at zero: the beamformer
+ * writes every voltage the integration reads); calls that overlap on the GPU -- two streams with no event between
+ * them -- race on it. */
+#define XENG_STATIC_SCRATCH_FLOAT2 (2u << 20)                       /* complex beam voltages */
+#define XENG_STATIC_SCRATCH_BYTES (8u * XENG_STATIC_SCRATCH_FLOAT2) /* 16 MiB */
+int xeng_beam_power_static(const void* d_in, const void* d_weights, void* d_out, int ninput, int nchan, int ntime,
+                           int nbeam, int ntime_sum, void* cuda_stream);
 int xeng_bf_set_tap(xeng_bf_t h, int on);
 /* Device pointer of the handle-owned cf32 [nchan][nbeam][ntime] voltage scratch (NULL until an
  * xeng_bf_run_integrate with the tap on has run). */
