@@ -38,6 +38,11 @@
 #ifndef XENG_CT_ABLATE
 #define XENG_CT_ABLATE 0
 #endif
+// developer timing builds only (results invalid): where the epilogue's bulk copies go.  1: every run starts on a
+// 128-byte line; 2: a warp's 8 runs of one quadrant are contiguous (4 KB) instead of one per triangle row
+#ifndef XENG_CT_PATTERN
+#define XENG_CT_PATTERN 0
+#endif
 
 namespace xeng {
 namespace {
@@ -82,6 +87,7 @@ constexpr int SMEM_BYTES = SMEM_HDR + RAW_STAGES * RAW_STAGE_BYTES + NSTAGE * ST
 static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 
 constexpr uint32_t IDESC = umma_idesc(2, 1, 1, 1, 1, 128, 256);
+constexpr uint32_t IDESC_N128 = umma_idesc(2, 1, 1, 1, 1, 128, 128);   // ablation 128 only
 
 // Tile order inside a channel: r = I*(I+1)/2 + J (J <= I).  (I, J) come from a constant table and (channel, r) are
 // walked incrementally, so that every value derived from the tile index is computed on the uniform datapath (no
@@ -288,10 +294,14 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
           for (int k = 0; k < 8; ++k) {
             const int n = min(diag ? (8 * q + k + 1) : PAIRS, ncell_max);
             if (k < nrow) {
-              if (a.accumulate) bulk_reduce_add_s32_elect(dst, src, n * 16);
-              else bulk_store_elect(dst, src, n * 16);
+              int32_t* d = dst;
+              if (XENG_CT_PATTERN == 1) d = reinterpret_cast<int32_t*>(reinterpret_cast<uintptr_t>(dst) & ~uintptr_t(127));
+              if (a.accumulate) bulk_reduce_add_s32_elect(d, src, n * 16);
+              else bulk_store_elect(d, src, n * 16);
             }
             ++rA1;
+            if (XENG_CT_PATTERN == 2) dst += PAIRS << 2;
+            else
             dst += rA1 << 2;           // next row pair of the triangle starts rA1+1 cells later
             src += RUN_STRIDE;
           }
@@ -333,6 +343,9 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
         const int rs = gs % RAW_STAGES, slot = gs % NSTAGE;
         XTRACE(grp, 0);
         const bool ldg_path = ABL && (ablate & 64);                    // ablation: global -> registers, no raw ring
+        // ablation 128 (timing only, results invalid): what a CTA pair with the B columns split would leave one CTA
+        // to do -- B loads / stores for half the columns, MMAs that read half of B
+        const bool halfB = (ablate & 128) != 0;
         if (!ldg_path) mbar_wait(&S->raw_full[rs], (gs / RAW_STAGES) & 1, a.err, 500 + rs);
         XTRACE(grp, 1);
         const uint32_t rbase = raw0 + rs * RAW_STAGE_BYTES;
@@ -353,8 +366,10 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
         if (live) {
           rawA0 = lds_v4(rbase + lds_a);
           rawA1 = lds_v4(rbase + lds_b);
-          rawB0 = lds_v4(rbase + boff + lds_a);
-          rawB1 = lds_v4(rbase + boff + lds_b);
+          if (!halfB || c < 2) {
+            rawB0 = lds_v4(rbase + boff + lds_a);
+            rawB1 = lds_v4(rbase + boff + lds_b);
+          }
         }
         // The TMA warp may refill the raw slot once the loads have RETURNED, not merely issued (SYNCS.ARRIVE does
         // not wait for outstanding LDS): make the arrive depend on one word of every load.
@@ -384,12 +399,14 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
             sts_v4(base + OFF_A_RE + stsA + SBO, reA1);
             sts_v4(base + OFF_A_IM + stsA, imA0);
             sts_v4(base + OFF_A_IM + stsA + SBO, imA1);
+            if (!halfB || c < 2) {
             sts_v4(base + OFF_B_IM + stsB, imB0);
             sts_v4(base + OFF_B_IM + stsB + 4 * SBO, imB1);
             sts_v4(base + OFF_B_RE + stsB, reB0);
             sts_v4(base + OFF_B_RE + stsB + 4 * SBO, reB1);
             sts_v4(base + OFF_B_NIM + stsB, nimB0);
             sts_v4(base + OFF_B_NIM + stsB + 4 * SBO, nimB1);
+            }
           }
         }
         XTRACE(grp, 4);
@@ -445,10 +462,11 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
             for (int j = 0; j < KB; ++j) {
               if (j < nkb) {
                 const uint32_t sj = sbase + j * (4 * KGRP_BYTES);
+                const uint32_t idesc = (ablate & 128) ? IDESC_N128 : IDESC;
                 umma_i8_ss(tmem_d, umma_smem_desc(sj + OFF_A_RE, KGRP_BYTES, SBO),
-                           umma_smem_desc(sj + OFF_B_RE, KGRP_BYTES, SBO), IDESC, (ks | j) != 0);
+                           umma_smem_desc(sj + OFF_B_RE, KGRP_BYTES, SBO), idesc, (ks | j) != 0);
                 umma_i8_ss(tmem_d, umma_smem_desc(sj + OFF_A_IM, KGRP_BYTES, SBO),
-                           umma_smem_desc(sj + OFF_B_IM, KGRP_BYTES, SBO), IDESC, 1);
+                           umma_smem_desc(sj + OFF_B_IM, KGRP_BYTES, SBO), idesc, 1);
               }
             }
           }
