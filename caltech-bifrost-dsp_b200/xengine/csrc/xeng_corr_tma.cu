@@ -43,6 +43,11 @@
 #ifndef XENG_CT_PATTERN
 #define XENG_CT_PATTERN 0
 #endif
+// fused CorrAcc: tiles ahead whose accumulator lines an epilogue warp pulls into L2 (prefetch.global.L2) before it
+// needs them, so that the bulk reduction finds them there instead of holding its staging buffer through an HBM read
+#ifndef XENG_CT_PREFETCH
+#define XENG_CT_PREFETCH 0
+#endif
 
 namespace xeng {
 namespace {
@@ -241,6 +246,29 @@ __global__ void __launch_bounds__(N_THREADS, 1) corr_swz_kernel(const __grid_con
         sub_le = a.sub_begin[tw.r * N_EPI_WARPS + warp + 1];
         if (sub_lb + lane < sub_le) sub_e0 = a.sub_entries[sub_lb + lane];
         if (sub_lb + 32 + lane < sub_le) sub_e1 = a.sub_entries[sub_lb + 32 + lane];
+      }
+      if (XENG_CT_PREFETCH > 0 && a.accumulate) {
+        // lane -> one of this warp's 32 runs (plane, quadrant half rb1, row pair k) of the tile XENG_CT_PREFETCH ahead
+        TileWalk pw = tw;
+#pragma unroll
+        for (int i = 0; i < XENG_CT_PREFETCH; ++i) pw.next(a);
+        if (pw.valid(a)) {
+          const Tile pt = pw.get();
+          const int pl = lane >> 4, rb1 = (lane >> 3) & 1, k = lane & 7;
+          const int pA0 = pt.J * PAIRS, prow = pt.I * PAIRS + 8 * q + k;
+          const int pn = min(pt.I == pt.J ? (8 * q + k + 1) : PAIRS, a.npairs - pA0);
+          if (prow < a.npairs && pn > 0) {
+            const long cell = (static_cast<long>(prow) * (prow + 1)) / 2 + pA0;
+            const char* p0 = reinterpret_cast<const char*>(a.out + static_cast<long>(pt.c) * a.words_per_chan +
+                                                           pl * plane_words +
+                                                           ((static_cast<long>(2 * b0 + rb1) * a.quad_cells + cell) << 2));
+            const char* pe = p0 + pn * 16;
+            const char* ln = reinterpret_cast<const char*>(reinterpret_cast<uintptr_t>(p0) & ~uintptr_t(127));
+#pragma unroll
+            for (int j = 0; j < 5; ++j, ln += 128)
+              if (ln < pe) asm volatile("prefetch.global.L2 [%0];" ::"l"(ln));
+          }
+        }
       }
       XTRACE(4, 0);
       mbar_wait(&S->tmem_full[buf], (it >> 1) & 1, a.err, 100 + buf);
