@@ -53,6 +53,11 @@ def parse():
                    help="gather dumps with dist.gather (NCCL kernels) instead of copy-engine peer writes")
     p.add_argument("--push", default="sm", choices=["sm", "ce"],
                    help="per-step products to rank 0: xeng_peer_push (SM stores) or cudaMemcpyAsync (copy engines)")
+    p.add_argument("--push-slots", type=int, default=4,
+                   help="N > 1: fast-dump buffers a rank may have in flight to rank 0 before its correlator waits")
+    p.add_argument("--dump-slices", type=int, default=None,
+                   help="N > 1: the long dump leaves for rank 0 in this many per-step slices of the next integration "
+                        "(default acc_gulps // 4; 0 = one burst)")
     p.add_argument("--cpu-seconds", type=float, default=15.0, help="budget for the cpu_baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-path-kernels", action="store_true", help="skip the per-kernel figures of the rest of the path")
@@ -469,15 +474,25 @@ def run_b200(args):
     d_in = [torch.randint(0, 256, (ntime, nchan, NINPUT), dtype=torch.uint8, device=dev, generator=g)
             for _ in range(NBUF)]
     gulps_host = [x.cpu().numpy() for x in d_in]
-    d_acc = torch.zeros(out_words, dtype=torch.int32, device=dev)
-    d_dump = torch.zeros(out_words, dtype=torch.int32, device=dev)
+    # CorrAcc's output ring: as in blocks/corr_block.py (acc_oring=) the fused launch accumulates straight into the
+    # span it will commit, so a finished integration is shipped from where it lies while the next one runs in the
+    # other span -- no snapshot copy on the correlator's stream
+    accs = [torch.zeros(out_words, dtype=torch.int32, device=dev) for _ in range(2)]
+    cur = [0]
+
+    def acc():
+        return accs[cur[0]]
+
+    d_dump = torch.zeros(out_words, dtype=torch.int32, device=dev) if world == 1 else None   # N = 1: the dump's destination
+    dumped = [None]
     gather_list = None
     stream = torch.cuda.Stream(device=dev)
     xc = ops.XCorr(nstand=NSTAND, npol=NPOL, nchan=nchan, ntime_gulp=ntime, gpu=local)
     xc.set_stream(stream)
     vm, cj = real_selection(ops, orc, np.random.default_rng(4704))
     xc.set_subsel(vm, cj, NSUM)
-    fast = [torch.zeros((nchan // NSUM, NVIS, 2), dtype=torch.int32, device=dev) for _ in range(2)]
+    NSLOT = max(2, args.push_slots)
+    fast = [torch.zeros((nchan // NSUM, NVIS, 2), dtype=torch.int32, device=dev) for _ in range(NSLOT)]
 
     def barrier():
         # synchronize on BOTH sides of the rendezvous: a rank's side-stream traffic (a 766 MB dump still streaming
@@ -489,7 +504,7 @@ def run_b200(args):
         torch.cuda.synchronize(dev)
 
     # ---- exchanges (N > 1): long dump -> PeerGather, per-step fast dump -> PeerStream; NCCL fallbacks
-    gstream = torch.cuda.Stream(device=dev) if world > 1 else None      # long dumps
+    gstream = torch.cuda.Stream(device=dev)                              # long dumps
     pstream = torch.cuda.Stream(device=dev) if world > 1 else None      # per-step pushes
     peer = fpush = None
     push_kind = None
@@ -497,7 +512,7 @@ def run_b200(args):
         if not args.nccl_gather:
             try:
                 peer = sharding.PeerGather(out_words, torch.int32, dev, dist, root=0)
-                fpush = sharding.PeerStream(fast[0].numel(), torch.int32, dev, dist, nslot=2, root=0, via=args.push)
+                fpush = sharding.PeerStream(fast[0].numel(), torch.int32, dev, dist, nslot=NSLOT, root=0, via=args.push)
             except Exception as e:                              # no symmetric memory on this node: all ranks use NCCL
                 sys.stderr.write("rank %d: symmetric-memory peer writes unavailable (%s)\n" % (rank, e))
                 peer = fpush = None
@@ -505,34 +520,64 @@ def run_b200(args):
         dist.all_reduce(agreed, op=dist.ReduceOp.MIN)
         if int(agreed) == 0:
             peer, args.nccl_gather = None, True
-            fpush = sharding.GatherStream(fast[0].numel(), torch.int32, dev, dist, nslot=2, root=0)
+            fpush = sharding.GatherStream(fast[0].numel(), torch.int32, dev, dist, nslot=NSLOT, root=0)
             push_kind = "NCCL dist.gather every step"
         else:
-            d_dump = peer.slot if rank == 0 else d_dump    # rank 0 snapshots straight into its own slot
             push_kind = ("peer writes into rank 0's symmetric-memory slots over NVLink (%s), no cross-rank wait"
                          % ("xeng_peer_push: SM stores from CTAs resident beside the correlator" if args.push == "sm"
                             else "cudaMemcpyAsync: copy engines"))
     if world > 1 and rank == 0 and args.nccl_gather:
-        gather_list = [d_dump] + [torch.empty_like(d_dump) for _ in range(world - 1)]
+        gather_list = [torch.empty_like(accs[0]) for _ in range(world)]
 
     def dump_device():
-        # CorrAcc's copy_array into its output span, then (N > 1) the gather of that span to rank 0 on a side
-        # stream: as in the pipeline, the correlator carries on with the next integration while the previous dump
-        # travels; the next dump waits for it, and so does the end of the timed region.
-        if world > 1:
-            stream.wait_stream(gstream)
-        d_dump.copy_(d_acc, non_blocking=True)
-        if world > 1:
-            gstream.wait_stream(stream)
-            with torch.cuda.stream(gstream):
-                if peer is not None:
-                    peer.push(d_dump)
-                else:
-                    sharding.gather_to_root(d_dump, dist, root=0, out=gather_list)
+        # The finished integration leaves from its span on a side stream -- N = 1: CorrAcc's copy_array into the
+        # consumer's buffer; N > 1: the gather to rank 0 -- while the correlator carries on with the next integration
+        # in the other span, as in the pipeline.  The next dump waits for this one (so a span is never reused while
+        # it travels), and so does the end of the timed region.
+        src = acc()
+        flush_dump()
+        stream.wait_stream(gstream)
+        dumped[0] = src
+        if peer is not None and nslices > 0:
+            # in slices, one per step of the next integration (dump_slice): 766 MB per rank in one burst fills the
+            # links into rank 0 for 7 ms at 8 ranks and the per-step products wait behind it (profiles/r02x)
+            pending["src"], pending["ranges"] = src, peer.slices(nslices)
+            dseq[0] += 1
+            return
+        gstream.wait_stream(stream)
+        with torch.cuda.stream(gstream):
+            if world == 1:
+                d_dump.copy_(src, non_blocking=True)
+            elif peer is not None:
+                peer.push(src)
+            else:
+                sharding.gather_to_root(src, dist, root=0, out=gather_list)
+
+    nslices = (accg // 4 if args.dump_slices is None else args.dump_slices) if world > 1 else 0
+    pending = {"src": None, "ranges": []}
+    dseq = [0]                                               # sliced dumps sent so far = the sequence word of the last
+
+    def dump_slice(after):
+        """The next slice of the travelling dump, on the dump stream, once the step that recorded `after` is done."""
+        lo, hi = pending["ranges"].pop(0)
+        with torch.cuda.stream(gstream):
+            gstream.wait_event(after)
+            peer.push_range(pending["src"], lo, hi)
+            if not pending["ranges"]:
+                peer.commit(dseq[0])                           # a sequence word behind the last slice: no rank waits
+                pending["src"] = None
+
+    def flush_dump():
+        """Whatever is left of a travelling dump leaves now (end of a timed region; a dump timed on its own)."""
+        if pending["src"] is not None:
+            ev = torch.cuda.Event()
+            ev.record(stream)
+            while pending["src"] is not None:
+                dump_slice(ev)
 
     push_launches = 2 if getattr(fpush, "via", None) == "sm" else 0
-    fast_done = [torch.cuda.Event() for _ in range(2)]
-    fast_free = [torch.cuda.Event() for _ in range(2)]
+    fast_done = [torch.cuda.Event() for _ in range(NSLOT)]
+    fast_free = [torch.cuda.Event() for _ in range(NSLOT)]
     counts = [0] * NBUF                                      # gulps of each buffer in the running integration
     nlaunch = [0]
     seqc = [0]
@@ -542,17 +587,18 @@ def run_b200(args):
         Returns the step's sequence number."""
         seq = seqc[0]
         seqc[0] += 1
-        if first:
+        if first:                                            # a new integration opens in the other span
+            cur[0] ^= 1
             for k in range(NBUF):
                 counts[k] = 0
         counts[k_buf] += 1
         if not fused_fast:
-            xc.accumulate(src, d_acc, first)
+            xc.accumulate(src, acc(), first)
             nlaunch[0] += 1
             return seq
-        slot = seq % 2
-        stream.wait_event(fast_free[slot])                   # the push of step seq - 2 has left this buffer
-        xc.accumulate_subsel(src, d_acc, first, fast[slot], True)
+        slot = seq % NSLOT
+        stream.wait_event(fast_free[slot])                   # the push of step seq - NSLOT has left this buffer
+        xc.accumulate_subsel(src, acc(), first, fast[slot], True)
         nlaunch[0] += 1
         fast_done[slot].record(stream)
         with torch.cuda.stream(pstream):
@@ -560,6 +606,8 @@ def run_b200(args):
             fpush.push(fast[slot], seq)
             nlaunch[0] += push_launches                      # xeng_peer_push: payload kernel + sequence-word kernel
             fast_free[slot].record(pstream)
+        if pending["src"] is not None:
+            dump_slice(fast_done[slot])
         return seq
 
     # ---- value: inputs resident in HBM
@@ -567,6 +615,7 @@ def run_b200(args):
         for i in range(Wm):
             launch_step(d_in[i % NBUF], i % NBUF, (i % accg) == 0)
         dump_device()          # warm the dump path too (first NCCL gather sets up its peer connections)
+        flush_dump()
     barrier()
     sampler = ClockSampler(local) if rank == 0 else None
     evs = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
@@ -589,8 +638,9 @@ def run_b200(args):
             if (g_i % accg) == accg - 1:
                 dump_device()
                 ndump += 1
+        flush_dump()
+        stream.wait_stream(gstream)
         if world > 1:
-            stream.wait_stream(gstream)
             stream.wait_stream(pstream)
         end = torch.cuda.Event(enable_timing=True)
         end.record(stream)
@@ -604,7 +654,7 @@ def run_b200(args):
     # what was timed is what the reference computes: two channel slabs of the accumulator the timed region left
     # behind against the oracle on the same bytes
     vchans = [0, nchan // 2 - 1] if nchan > 2 else [0]
-    verified = verify_accumulator(orc, d_acc, nchan, wpc, counts, gulps_host, vchans)
+    verified = verify_accumulator(orc, acc(), nchan, wpc, counts, gulps_host, vchans)
     fast_verified = None
     if fused_fast:                                           # and the last fast dump, every channel group
         last = last_seq
@@ -612,7 +662,7 @@ def run_b200(args):
         sub_ch = [0, 1, 2, 3]                                # first output channel = input channels 0..3
         v4 = np.ascontiguousarray(gulps_host[(K - 1) % NBUF][:, sub_ch]).reshape(ntime, 4, NSTAND, NPOL)
         x_last = orc.corr_xgpu(v4)
-        fast_verified = bool(np.array_equal(fast[last % 2][0].cpu().numpy(), orc.subselect(x_last, vm, cj, NSUM)[0]))
+        fast_verified = bool(np.array_equal(fast[last % NSLOT][0].cpu().numpy(), orc.subselect(x_last, vm, cj, NSUM)[0]))
     if not verified or fast_verified is False:
         raise RuntimeError("timed accumulator / fast dump differ from the oracle on the same voltages")
 
@@ -623,14 +673,14 @@ def run_b200(args):
         dmp1 = torch.cuda.Event(enable_timing=True)
         dmp0.record(stream)
         dump_device()
-        if world > 1:
-            stream.wait_stream(gstream)
+        flush_dump()
+        stream.wait_stream(gstream)
         dmp1.record(stream)
     barrier()
     dump_ms = dmp0.elapsed_time(dmp1)
     # what a dump costs when it travels beside the correlator, as it does at its true cadence: M steps with one dump
     # launched on the side stream at their start, against the same M steps alone (M steps outlast the dump)
-    M = max(8, int(1.5 * dump_ms / max(kern_ms, 1e-3)) + 4)
+    M = max(8, int(1.5 * dump_ms / max(kern_ms, 1e-3)) + 4, nslices + 4)
     if world > 1:                                              # the same number of steps (and pushes) on every rank
         mt = torch.tensor([M], device=dev)
         dist.all_reduce(mt, op=dist.ReduceOp.MAX)
@@ -644,10 +694,11 @@ def run_b200(args):
             a0.record(stream)
             if with_dump:
                 dump_device()
-            for j in range(M):
-                launch_step(d_in[j % NBUF], j % NBUF, False)
+            for j in range(M):                                  # j = 0 opens the next integration in the other span
+                launch_step(d_in[j % NBUF], j % NBUF, j == 0)
+            flush_dump()
+            stream.wait_stream(gstream)
             if world > 1:
-                stream.wait_stream(gstream)
                 stream.wait_stream(pstream)
             a1.record(stream)
         barrier()
@@ -662,8 +713,9 @@ def run_b200(args):
             fpush.finish()
         torch.cuda.synchronize(dev)
         last = seqc[0] - 1                                   # the most recent step of all (the dump-overlap runs above)
-        probe = torch.stack([d_dump[:4096].to(torch.int64).sum(), d_dump[-4096:].to(torch.int64).sum(),
-                             fast[last % 2].to(torch.int64).sum(), fast[last % 2][-1].to(torch.int64).sum()])
+        sent_dump = dumped[0]
+        probe = torch.stack([sent_dump[:4096].to(torch.int64).sum(), sent_dump[-4096:].to(torch.int64).sum(),
+                             fast[last % NSLOT].to(torch.int64).sum(), fast[last % NSLOT][-1].to(torch.int64).sum()])
         sent = [torch.empty_like(probe) for _ in range(world)]
         dist.all_gather(sent, probe)
         if rank == 0:
@@ -671,6 +723,8 @@ def run_b200(args):
             gather_ok = all(bool((torch.stack([got[r][:4096].to(torch.int64).sum(),
                                                got[r][-4096:].to(torch.int64).sum()]) == sent[r][:2]).all())
                             for r in range(world))
+            if peer is not None and nslices > 0:             # ... and every rank's last slice is in (sequence words)
+                gather_ok = gather_ok and bool((peer.arrived() == dseq[0] % 4096).all())
             payload, seqs = fpush.slot_on_root(last)
             payload = payload.view(world, nchan // NSUM, NVIS, 2)
             push_ok = bool((seqs == last).all()) and all(
@@ -715,7 +769,11 @@ def run_b200(args):
                 launch_step(ring[slot], i % 2, (i % accg) == 0)
                 freed[slot].record(stream)
                 if (i % accg) == accg - 1 or j == n - 1:
-                    h_out.copy_(d_acc, non_blocking=True)      # CorrAcc dump into a cuda_host ring span
+                    src = acc()                                # CorrAcc dump into a cuda_host ring span, side stream
+                    stream.wait_stream(gstream)
+                    gstream.wait_stream(stream)
+                    with torch.cuda.stream(gstream):
+                        h_out.copy_(src, non_blocking=True)
                     d2h += out_words * 4
         return d2h
 
@@ -730,6 +788,7 @@ def run_b200(args):
     copy_stream.wait_event(t0)
     d2h_total = e2e_steps(K, n_e2e_warm)
     stream.wait_stream(copy_stream)
+    stream.wait_stream(gstream)
     if world > 1:
         stream.wait_stream(pstream)
     t1.record(stream)
@@ -751,7 +810,7 @@ def run_b200(args):
     # ---- whole X-engine (row N1) on the same process group
     full = None
     if not args.no_xengine_full:
-        full = xengine_full(torch, dist, ops, sharding, orc, args, dev, world, rank, xc, d_in, gulps_host, d_acc, fast,
+        full = xengine_full(torch, dist, ops, sharding, orc, args, dev, world, rank, xc, d_in, gulps_host, acc(), fast,
                             vm, cj, stream, h_in, barrier)
 
     # ---- max over ranks (+ every rank's own per-step figures on rank 0)
@@ -832,9 +891,13 @@ def run_b200(args):
                      "gather": None if world == 1 else ("NCCL dist.gather" if args.nccl_gather else
                                                         "peer writes into rank 0's symmetric-memory buffer (copy engines over NVLink)"),
                      "bytes_to_rank0": (world - 1) * out_words * 4,
+                     "slices": nslices,
                      "note": "dumps fall at their true cadence (every acc_gulps steps); alone_ms is one dump "
-                             "(device copy + gather to rank 0) timed with nothing to overlap; overlapped_cost_ms is "
-                             "what a dump adds to a run of steps it travels beside (side stream, copy engines), "
+                             "(the finished span's copy to its consumer: N = 1 a device copy, N > 1 the gather to rank "
+                             "0; side stream, the correlator accumulates the next integration in the other span of "
+                             "the output ring) timed with nothing to overlap; overlapped_cost_ms is "
+                             "what a dump adds to a run of steps it travels beside (side stream, copy engines; N > 1: "
+                             "in `slices` pieces, one behind each of the next steps), "
                              "measured as (M steps + 1 dump) - (M steps), max over ranks; when no dump falls inside "
                              "the timed region its share overlapped_cost_ms * steps / acc_gulps is ADDED to the "
                              "timed total before value and ms_per_step are formed"},

@@ -78,6 +78,13 @@ class PeerGather(object):
         self.hdl = symm_mem.rendezvous(self.buf, dist.group.WORLD.group_name)
         self.root_buf = self.hdl.get_buffer(root, (self.world * n,), dtype)
         self.slot = self.root_buf[self.rank * n:(self.rank + 1) * n]
+        # one sequence word per rank on root: a producer that ends a dump with commit(seq) never waits for its peers
+        import torch
+        self.seqbuf = symm_mem.empty(self.world, dtype=torch.int64, device=device)
+        self.seqbuf.fill_(-1)
+        self.seq_hdl = symm_mem.rendezvous(self.seqbuf, dist.group.WORLD.group_name)
+        self.root_seq = self.seq_hdl.get_buffer(root, (self.world,), torch.int64)
+        self.numbers = torch.arange(1 << 12, dtype=torch.int64, device=device)
 
     def push(self, src):
         """Enqueue on the current stream: this rank's ``src`` into its slot on root, then the barrier.  After the
@@ -91,6 +98,37 @@ class PeerGather(object):
             for i in range(0, flat.numel(), step):
                 _ce_copy(self.slot[i:i + step], flat[i:i + step])
         self.hdl.barrier(channel=0)
+
+    def slices(self, nslices, align=4096):
+        """Element ranges [(lo, hi), ...] that cut one rank's buffer into ``nslices`` pieces (multiples of ``align``)."""
+        per = -(-self.n // max(1, nslices))
+        per = -(-per // align) * align
+        return [(lo, min(self.n, lo + per)) for lo in range(0, self.n, per)]
+
+    def push_range(self, src, lo, hi):
+        """Enqueue on the current stream: elements [lo, hi) of this rank's ``src`` into its slot on root (copy engines).
+        A long dump need not leave in one burst: sent as one slice per step of the NEXT integration it shares the
+        link with the per-step products instead of standing in their way; ``commit()`` after the last slice."""
+        flat = src.reshape(-1)
+        step = max(1, self.chunk_bytes // flat.element_size())
+        for i in range(lo, hi, step):
+            j = min(hi, i + step)
+            _ce_copy(self.slot[i:j], flat[i:j])
+
+    def commit(self, seq=None):
+        """Ends a sliced push.  ``seq=None``: a symmetric-memory barrier -- after it (in stream order, on root)
+        ``parts()`` holds every rank's data, but every rank's stream waits for the slowest one, with a spinning
+        kernel (r02z, 8 ranks: 5 steps at twice their time on the ranks that got there first).  ``seq=k``: this
+        rank's sequence word on root becomes ``k`` after its last slice (copy engine, stream order); nobody waits, the
+        consumer on root reads ``arrived()``."""
+        if seq is None:
+            self.hdl.barrier(channel=0)
+        else:
+            _ce_copy(self.root_seq[self.rank], self.numbers[seq % self.numbers.numel()])
+
+    def arrived(self):
+        """Root only: the sequence word of every rank's last committed dump, int64 [world]."""
+        return self.seqbuf if self.rank == self.root else None
 
     def parts(self):
         """Rank-ordered views of the gathered slabs (root only)."""

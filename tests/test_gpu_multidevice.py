@@ -76,3 +76,18 @@ def test_peer_push_payload_then_sequence_word():
                 lambda: ops.peer_push(dst, src, 20, None, 0, stream)):
         with pytest.raises(XengError):
             bad()
+
+
+def test_peer_exchanges_two_ranks():
+    """PeerStream / PeerGather (torch symmetric memory over NVLink) between two ranks, one per GPU."""
+    import os
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    here = os.path.dirname(os.path.abspath(__file__))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29533", os.path.join(here, "peer_worker.py")]
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=240)
+    assert res.returncode == 0, res.stdout.decode("utf-8", "replace")[-4000:]
