@@ -345,7 +345,18 @@ def path_kernels(torch, ops, dev, nchan, hbm_peak, iters=10):
     res["corr_store"] = {"ms": ms_store, "gsamples_per_s": ntime * nchan * NINPUT / ms_store / 1e6}
     res["corr_acc_subsel_fused"]["unfused_ms"] = ms_store + res["corr_acc"]["ms"] + res["corr_subsel_4704"]["ms"]
     xc.close()
-    del gulps, acc2, fast
+    # a span of five gulps in ONE launch (ntime 2400, Corr's constructor default acc_len, corr_block.py:221): one
+    # accumulator read-modify-write per 2400 samples instead of five -- the tensor-bound regime of the same kernel
+    nt5 = 5 * ntime
+    span = torch.randint(0, 256, (nt5, nchan, NINPUT), dtype=torch.uint8, device=dev)
+    xc5 = ops.XCorr(nstand=NSTAND, npol=NPOL, nchan=nchan, ntime_gulp=nt5)
+    ms5 = timeit(lambda: xc5.accumulate(span, acc2, False), 10)
+    ops5 = 8.0 * 248512 * nchan * nt5
+    res["corr_acc_span_2400"] = {"ms": ms5, "gsamples_per_s": nt5 * nchan * NINPUT / ms5 / 1e6,
+                                 "useful_int8_tops": ops5 / ms5 / 1e9, "frac_int8_nominal": ops5 / ms5 / 1e9 / INT8_NOMINAL_TOPS,
+                                 "note": "five 480-sample gulps per launch: not the headline's configuration"}
+    xc5.close()
+    del gulps, acc2, fast, span
     # ingest: one gulp of SNAP2 packets (96 ch x 64 inputs each, 22 per spectrum) -> voltage buffer
     ncp, npp, stride = 96, 64, 32 + 96 * 64
     npk = ntime * (nchan // ncp) * (NINPUT // npp)
