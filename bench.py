@@ -564,7 +564,7 @@ def run_b200(args):
             else:
                 sharding.gather_to_root(src, dist, root=0, out=gather_list)
 
-    nslices = (accg // 4 if args.dump_slices is None else args.dump_slices) if world > 1 else 0
+    nslices = (accg // 4 if args.dump_slices is None else args.dump_slices) if peer is not None else 0
     pending = {"src": None, "ranges": []}
     dseq = [0]                                               # sliced dumps sent so far = the sequence word of the last
 
