@@ -87,3 +87,15 @@ def test_gather_dumps_two_gloo_ranks():
     for p in procs:
         p.join(timeout=60)
     assert res == [(0, "ok"), (1, "ok")], res
+
+
+def test_peer_gather_slices_cover_the_buffer_exactly():
+    """PeerGather.slices: the per-step pieces a long dump leaves in -- contiguous, aligned, covering [0, n) once."""
+    from xengine import sharding
+    for n, k in ((2 * 384 * 249216, 62), (1000, 7), (4096, 1), (5, 3), (3 * 1000 * 1000 + 16, 7)):
+        pg = object.__new__(sharding.PeerGather)
+        pg.n = n
+        r = pg.slices(k)
+        assert r[0][0] == 0 and r[-1][1] == n and len(r) <= max(1, k)
+        assert all(a[1] == b[0] for a, b in zip(r, r[1:]))
+        assert all(lo % 4096 == 0 and hi > lo for lo, hi in r)
