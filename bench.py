@@ -427,6 +427,17 @@ def path_kernels(torch, ops, dev, nchan, hbm_peak, iters=10):
     res["upchan_beamform_fused"] = {"ms": ms, "alg_bytes": ab, "gbs": ab / ms / 1e6,
                                     "frac_hbm": ab / ms / 1e6 / hbm_peak, "gsamples_per_s": nsamp / ms / 1e6,
                                     "config": "%d frames x %d fine x %d ch x %d inputs, %d beams" % (nfr, nf, nch_u, NINPUT, nb_u)}
+    del vu, xu, wu, ou
+    # the imaging script's correlate (lwa352-upchan-imag.py:85-106): 480 samples at NUPCHAN = 2 = 240 frames, the first
+    # 192 merged frequencies, complex fp32 Hermitian update on the FMA pipe
+    nfr_c, nfq_c = 240, 192
+    xc_in = torch.randn((nfr_c, nfq_c, NINPUT, 2), dtype=torch.float32, device=dev)
+    xc_out = torch.zeros((nfq_c, NINPUT, NINPUT, 2), dtype=torch.float32, device=dev)
+    ms = timeit(lambda: ops.upchan_correlate(xc_in, xc_out, nfr_c, nfq_c, NINPUT, False), 4)
+    T_ = (NINPUT + 63) // 64
+    fl = 8.0 * nfr_c * nfq_c * (T_ * (T_ + 1) // 2) * 64 * 64
+    res["upchan_correlate"] = {"ms": ms, "tflops_fp32": fl / ms / 1e9, "gsamples_per_s": nfr_c * nfq_c * NINPUT / ms / 1e6,
+                               "config": "%d frames x %d freqs x %d inputs, accumulating" % (nfr_c, nfq_c, NINPUT)}
     return res
 
 

@@ -44,6 +44,7 @@ SIGNATURES = {
     "xeng_snap2_assemble": (_i, [_vp, _i, _i64, _vp, _u64, _i, _i, _i, _i, _i, _vp, _vp]),
     "xeng_upchan_fft": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "xeng_upchan_beamform": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "xeng_upchan_correlate": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
     "xeng_subsel_packets": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _i, _vp]),
     "xeng_reorder_packets": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _i, _vp]),
     "xeng_memcpy_async": (_i, [_vp, _vp, _sz, _vp]),

@@ -490,6 +490,17 @@ int xeng_upchan_beamform(const void* d_in, const void* d_weights, void* d_out, i
   return XENG_OK;
 }
 
+int xeng_upchan_correlate(const void* d_in, void* d_out, int nframe, int nfreq, int ninput, int first, void* stream) {
+  if (!d_in || !d_out) return fail(XENG_ERR_ARG, "null pointer");
+  if (nframe < 0 || nfreq <= 0 || ninput <= 0) return fail(XENG_ERR_ARG, "bad sizes");
+  if (nfreq > 65535) return fail(XENG_ERR_ARG, "at most 65535 frequencies per call, got %d", nfreq);
+  if ((reinterpret_cast<uintptr_t>(d_in) & 7) || (reinterpret_cast<uintptr_t>(d_out) & 7))
+    return fail(XENG_ERR_ARG, "cf32 buffers must be 8-byte aligned");
+  XENG_CUDA(xeng::launch_upchan_correlate(static_cast<const float2*>(d_in), static_cast<float2*>(d_out), nframe, nfreq,
+                                          ninput, first ? 1 : 0, static_cast<cudaStream_t>(stream)));
+  return XENG_OK;
+}
+
 int xeng_memcpy_async(void* dst, const void* src, size_t nbytes, void* stream) {
   if (!dst || !src) return fail(XENG_ERR_ARG, "null pointer");
   if (nbytes == 0) return XENG_OK;

@@ -132,5 +132,7 @@ cudaError_t launch_upchan_fft(const uint8_t* in, float2* out, long nframe, int n
                               cudaStream_t stream);
 cudaError_t launch_upchan_beamform(const uint8_t* in, const float2* w, float2* out, long nframe, int nfine, int nchan,
                                    int ninput, int nbeam, cudaStream_t stream);
+cudaError_t launch_upchan_correlate(const float2* in, float2* out, int nframe, int nfreq, int ninput, int first,
+                                    cudaStream_t stream);
 
 }  // namespace xeng

@@ -136,6 +136,14 @@ def upchan_beamform(d_in, d_weights, d_out, nframe, nfine, nchan, ninput, nbeam,
                                            int(ninput), int(nbeam), ptr(stream)), "xeng_upchan_beamform")
 
 
+def upchan_correlate(d_in, d_out, nframe, nfreq, ninput, first=True, stream=None):
+    """lwa352-upchan-imag.py:93-106's blocks.correlate on the upchannelised voltages: d_out[f][i][j] (=|+=)
+    sum_t d_in[t][f][i] * conj(d_in[t][f][j]) for the 64 x 64 tiles on or below the diagonal.  cf32 device buffers:
+    d_in [nframe][nfreq][ninput], d_out [nfreq][ninput][ninput]."""
+    check(_lib.load().xeng_upchan_correlate(ptr(d_in), ptr(d_out), int(nframe), int(nfreq), int(ninput),
+                                            int(bool(first)), ptr(stream)), "xeng_upchan_correlate")
+
+
 def subsel_packets(d_in, d_out, d_vismap, d_conj, nvis, nchan, nchan_sum, wpc, layout=PAYLOAD_PY, stream=None):
     """bfXgpuSubSelect written in CorrOutputPart's packet order (corr_output_part_block.py:378-391, 429-463):
     COR = int32 [nvis/4][nchan/nchan_sum][4][2]; PY = big-endian int32 [nvis][nchan/nchan_sum][2]."""

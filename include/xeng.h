@@ -143,6 +143,15 @@ int xeng_upchan_fft(const void* d_in, void* d_out, int nframe, int nfine, int nc
  * d_out cf32 [nframe][nbeam][nchan][nfine]. */
 int xeng_upchan_beamform(const void* d_in, const void* d_weights, void* d_out, int nframe, int nfine, int nchan,
                          int ninput, int nbeam, void* cuda_stream);
+/* The correlate half of the offline imaging script (scripts/lwa352-upchan-imag.py:93-106): stock bifrost
+ * blocks.correlate(nframe_per_integration=...) on the upchannelised, frequency-merged voltages.  d_in cf32
+ * [nframe][nfreq][ninput] (xeng_upchan_fft's XENG_UPCHAN_FREQ_MERGED output, or a frequency slice of it);
+ * d_out cf32 [nfreq][ninput][ninput]: element (i, j), j <= i, (=|+=) sum_t v[t][f][i] * conj(v[t][f][j]) -- first != 0
+ * starts an integration, first == 0 adds this gulp's frames to it.  64 x 64 tiles on or below the diagonal are written
+ * (diagonal tiles whole); the rest of the upper triangle is not touched.  bifrost is an absent submodule: the
+ * conjugation convention is the reference correlator's own (corr_output_full_block.py:582-591), parity unpinned. */
+int xeng_upchan_correlate(const void* d_in, void* d_out, int nframe, int nfreq, int ninput, int first,
+                          void* cuda_stream);
 
 /* Plain asynchronous copy between any two addresses of the unified address space (device, pinned host, a peer
  * GPU's memory mapped into this process) on `cuda_stream`: cudaMemcpyAsync(cudaMemcpyDefault), i.e. the COPY ENGINES.

@@ -403,6 +403,15 @@ def upchan_beamform(v_u8, weights):
     return np.einsum("bcik,fcik->fbck", np.asarray(weights).astype(np.complex128), X, optimize=True)
 
 
+def upchan_correlate(X):
+    """pipeline/scripts/lwa352-upchan-imag.py:93-106: bifrost's stock blocks.correlate on the upchannelised,
+    frequency-merged voltages (absent submodule; conjugation as the reference's own correlator checks,
+    check_golden_inputs.py:64-92 / corr_output_full_block.py:582-591: v_i * conj(v_j)).  X complex
+    [nframe, nfreq, ninput].  Returns complex128 [nfreq, ninput, ninput] (the full Hermitian matrix)."""
+    X = np.asarray(X).astype(np.complex128)
+    return np.einsum("tfi,tfj->fij", X, np.conj(X), optimize=True)
+
+
 def offline_beam_weights(freqs, delays_ns, weighting=None):
     """BfOfflineWeightsBlock.compute_weights, the part after the astropy pointing
     (beamform_offline_block.py:126-134): delays are made relative to the largest one, scaled by the per-input

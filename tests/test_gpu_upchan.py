@@ -126,3 +126,55 @@ def test_upchan_argument_errors(torch_cuda):
         ops.upchan_fft(v, o, 1, 4, 1, 4, 7)    # unknown layout
     with pytest.raises(RuntimeError):
         ops.upchan_beamform(v, None, o, 1, 4, 1, 4, 1)
+
+
+def _lower_tiles_mask(ninput, tile=64):
+    """Elements xeng_upchan_correlate writes: the 64 x 64 tiles on or below the diagonal."""
+    i = np.arange(ninput)
+    return (i[:, None] // tile) >= (i[None, :] // tile)
+
+
+@pytest.mark.parametrize("shape", [
+    (240, 6, 704),      # the imaging script's gulp: 480 samples at NUPCHAN = 2 (lwa352-upchan-imag.py:85-86), 6 of its 192 freqs
+    (15, 5, 70),        # 32 fine channels, ragged inputs
+    (1, 2, 64),         # a single frame
+    (33, 3, 130),       # frames not a multiple of the chunk, inputs two tiles and a bit
+])
+def test_upchan_correlate_matches_oracle_and_accumulates(torch_cuda, shape):
+    torch = torch_cuda
+    from xengine import ops
+    nframe, nfreq, ninput = shape
+    rng = np.random.default_rng(nframe * 7 + ninput)
+    nfine = 2
+    # genuine upchannelised voltages: the FFT kernel's frequency-merged output feeds the correlator, as in the script
+    v = _edge_bytes(rng.integers(0, 256, size=(2, nframe, nfine, (nfreq + 1) // 2, ninput), dtype=np.uint8))
+    mask = _lower_tiles_mask(ninput)
+    out = torch.full((nfreq, ninput, ninput, 2), float("nan"), dtype=torch.float32, device="cuda")
+    want = np.zeros((nfreq, ninput, ninput), dtype=np.complex128)
+    for g in range(2):                                  # two gulps of one integration: first, then accumulate
+        nchan = v.shape[3]
+        X = torch.empty((nframe, nchan * nfine, ninput, 2), dtype=torch.float32, device="cuda")
+        ops.upchan_fft(torch.from_numpy(v[g]).cuda(), X, nframe, nfine, nchan, ninput, ops.UPCHAN_FREQ_MERGED)
+        Xs = X[:, :nfreq].contiguous()                  # FrequencySelectBlock: the first nfreq merged channels
+        ops.upchan_correlate(Xs, out, nframe, nfreq, ninput, first=(g == 0))
+        want += orc.upchan_correlate(orc.upchannelize(v[g], "freq_merged").reshape(nframe, nchan * nfine, ninput)[:, :nfreq])
+    torch.cuda.synchronize()
+    got = _cplx(out)
+    assert np.isfinite(got[:, mask]).all()
+    assert np.isnan(got[:, ~mask].real).all()           # the rest of the upper triangle is not touched
+    err = np.abs(got[:, mask] - want[:, mask]).max(axis=1) / np.abs(want[:, mask]).max(axis=1)
+    assert err.max() <= TOL
+    # Hermitian where both halves exist (diagonal tiles), real non-negative autocorrelations
+    d = np.arange(ninput)
+    assert (got[:, d, d].real >= 0).all() and (np.abs(got[:, d, d].imag) <= TOL * got[:, d, d].real + 1e-30).all()
+
+
+def test_upchan_correlate_refuses_bad_arguments(torch_cuda):
+    torch = torch_cuda
+    from xengine import ops
+    from xengine._lib import XengError
+    x = torch.zeros(64, dtype=torch.float32, device="cuda")
+    with pytest.raises(XengError):
+        ops.upchan_correlate(x, x, 1, 0, 4)
+    with pytest.raises(XengError):
+        ops.upchan_correlate(x, None, 1, 1, 4)

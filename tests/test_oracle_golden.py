@@ -226,3 +226,15 @@ def test_snap2_oracle_against_the_reference_transmitter(golden_dir):
     assert k == len(pkts)
     out, ngood = orc.snap2_assemble([p.tobytes() for p in pkts], 0, ntime, nchan, nstand * npol)
     assert ngood == len(pkts) and np.array_equal(out, data.reshape(ntime, nchan, nstand * npol))
+
+
+def test_upchan_correlate_oracle_is_hermitian_and_linear_in_frames():
+    """orc.upchan_correlate (parity unpinned by reference vectors: bifrost's correlate block is an absent submodule):
+    Hermitian, diagonal = summed power, and the sum over two halves of the frames equals the whole."""
+    rng = np.random.default_rng(5)
+    X = rng.standard_normal((12, 3, 10)) + 1j * rng.standard_normal((12, 3, 10))
+    C = orc.upchan_correlate(X)
+    assert np.allclose(C, np.conj(C.transpose(0, 2, 1)))
+    assert np.allclose(C[:, np.arange(10), np.arange(10)].real, (np.abs(X) ** 2).sum(axis=0))
+    assert np.allclose(C, orc.upchan_correlate(X[:5]) + orc.upchan_correlate(X[5:]))
+    assert np.allclose(C[1, 2, 7], (X[:, 1, 2] * np.conj(X[:, 1, 7])).sum())
