@@ -726,9 +726,30 @@ def run_b200(args):
         barrier()
         return a0.elapsed_time(a1)
 
+    # the same M steps with no exchange at all (same launch, the fast dump stays on the GPU), before AND after the runs
+    # with exchanges: a GPU under sw_power_cap slows by several per cent over the first ~100 ms of load, and a
+    # one-sided comparison would charge that drift to the pushes
+    def alone_steps():
+        if not fused_fast:
+            return None
+        barrier()
+        b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            xc.accumulate_subsel(d_in[0], acc(), True, scratch_fast, True)
+            b0.record(stream)
+            for j in range(M):
+                xc.accumulate_subsel(d_in[j % NBUF], acc(), False, scratch_fast, True)
+            b1.record(stream)
+        barrier()
+        return b0.elapsed_time(b1)                           # (that integration is scrap: the next run opens a fresh one)
+
+    scratch_fast = torch.zeros_like(fast[0])
+    t_alone_before = alone_steps()
     t_plain = m_steps(False)
     t_dump = m_steps(True)
     dump_overlapped_ms = max(0.0, t_dump - t_plain)
+    t_alone_after = alone_steps() if dumped[0] is not acc() else None
+    t_alone = None if t_alone_before is None else 0.5 * (t_alone_before + (t_alone_after or t_alone_before))
     gather_ok = push_ok = None
     if world > 1:                                           # what arrived on rank 0 is what each rank sent
         with torch.cuda.stream(pstream):
@@ -839,8 +860,9 @@ def run_b200(args):
     amort_ms = 0.0 if ndump > 0 else dump_overlapped_ms * K / accg   # no long dump fell in the timed region: charge its share
     per_rank = None
     if world > 1:
-        t = torch.tensor([total_ms, e2e_ms, kern_ms, dump_ms, h2d_probe_gbs, dump_overlapped_ms], dtype=torch.float64,
-                         device=dev)
+        t = torch.tensor([total_ms, e2e_ms, kern_ms, dump_ms, h2d_probe_gbs, dump_overlapped_ms, t_alone or 0.0,
+                          t_plain, t_dump, t_alone_before or 0.0, t_alone_after or t_alone_before or 0.0],
+                         dtype=torch.float64, device=dev)
         allt = [torch.empty_like(t) for _ in range(world)]
         dist.all_gather(allt, t)
         sv = torch.tensor(step_ms, dtype=torch.float64, device=dev)
@@ -854,6 +876,7 @@ def run_b200(args):
         m = torch.stack(allt).max(dim=0).values
         total_ms, e2e_ms, kern_ms, dump_ms = [float(x) for x in m[:4].tolist()]
         dump_overlapped_ms = float(m[5])
+        t_alone, t_plain, t_dump, ta_b, ta_a = float(m[6]), float(m[7]), float(m[8]), float(m[9]), float(m[10])
         amort_ms = 0.0 if ndump > 0 else dump_overlapped_ms * K / accg
 
     if rank == 0:
@@ -939,6 +962,15 @@ def run_b200(args):
         if world > 1:
             line["fast_dump_push"] = {"every_step": True, "bytes_per_rank_per_step": fast[0].numel() * 4,
                                       "how": push_kind, "verified_on_rank0": push_ok, "in_timed_region": K}
+            line["exchange_overhead"] = {
+                "steps": M, "ms_per_step_no_exchange": t_alone / M,
+                "ms_per_step_no_exchange_before_after": [ta_b / M, ta_a / M], "ms_per_step_with_pushes": t_plain / M,
+                "ms_per_step_with_pushes_and_one_dump": t_dump / M,
+                "note": "the same M launches (fused Corr+CorrAcc+CorrSubsel, 384 ch) with the fast dump left on the GPU, "
+                        "pushed to rank 0 every step, and pushed while one long dump travels; max over ranks.  The "
+                        "no-exchange run is made before and after the other two: under sw_power_cap the same launch "
+                        "slows by several per cent over the first ~100 ms of load, which is larger than anything the "
+                        "exchanges add"}
             line["per_rank"] = per_rank
         if full is not None:
             line["xengine_full"] = full
