@@ -952,6 +952,11 @@ def run_b200(args):
                          "traffic_source": traffic_src,
                          "peak_source": peak_src, "alg_bytes_per_launch": alg_bytes, "kernel_ms": kern_ms,
                          "kernel_ms_is": "median over the timed steps of the CUDA-event interval around one launch",
+                         "reduce_path": {"payload_gbs": out_words * 4 / kern_ms / 1e6,
+                                         "ceiling_gbs": 2600.0, "frac": out_words * 4 / kern_ms / 1e6 / 2600.0,
+                                         "ceiling_source": "profiles/r03o_bulk_pattern.txt: cp.reduce.async.bulk.add.s32 "
+                                                           "from 148 SMs into a > L2 footprint, wall clock; the fused "
+                                                           "accumulate's read-modify-write goes through this path"},
                          "tensor": {"useful_int8_tops": useful_tops, "nominal_peak_tops": INT8_NOMINAL_TOPS,
                                     "frac_nominal": useful_tops / INT8_NOMINAL_TOPS,
                                     "measured_int8_gemm_tops": int8_meas,

@@ -27,7 +27,7 @@
 // Why this shape (measurements: profiles/r01c_*, scripts/trace.py, scripts/ubench/bulk_rate.cu): a warp can issue one
 // bulk copy per ~80 cycles, so the 220 copies of a tile need >= 4 warps issuing concurrently; one MMA-issuing thread
 // needs >= 4 MMAs per barrier round trip to keep the tensor pipe fed; the bulk-reduce path itself sustains
-// 3.17 TB/s of payload (= HBM read + write), i.e. the HBM roofline.
+// ~2.6 TB/s of payload by the wall clock (= 5.2 TB/s of HBM read + write; profiles/r03o_bulk_pattern.txt).
 //
 // Roles (832 threads): warps 0-7 epilogue, 8-15 unpack group 0, 16-23 unpack group 1, 24 TMA producer, 25 MMA issuer.
 #include <cuda.h>
