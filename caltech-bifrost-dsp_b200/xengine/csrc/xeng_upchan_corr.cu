@@ -8,8 +8,8 @@
 // -- PARITY UNPINNED by reference vectors, checked against the float64 oracle.
 //
 // The voltages are FFT outputs (not integers), so this runs on the fp32 FMA pipe: 64 x 64 output tiles, 256 threads,
-// 4 x 4 complex accumulators per thread, 16-frame chunks staged in shared memory with the next chunk's global loads in
-// flight.  Only tiles on or below the diagonal are computed and written (diagonal tiles are written whole).
+// 4 x 4 complex accumulators per thread, 16-frame chunks double-buffered in shared memory with the next chunk's global
+// loads in flight.  Only tiles on or below the diagonal are computed and written (diagonal tiles are written whole).
 #include "xeng_internal.h"
 
 namespace xeng {
@@ -21,8 +21,8 @@ constexpr int UC_THREADS = 256;
 
 __global__ void __launch_bounds__(UC_THREADS) upchan_correlate_kernel(const float2* __restrict__ in, float2* __restrict__ out,
                                                                        int nframe, int nfreq, int ninput, int first) {
-  __shared__ float2 As[UC_K][UC_T];
-  __shared__ float2 Bs[UC_K][UC_T];
+  __shared__ float2 As[2][UC_K][UC_T];      // double buffered: one barrier per chunk
+  __shared__ float2 Bs[2][UC_K][UC_T];
   int I = 0, p = blockIdx.x;            // tile pair index p = I (I + 1) / 2 + J, J <= I
   while (p > I) {
     p -= I + 1;
@@ -54,22 +54,23 @@ __global__ void __launch_bounds__(UC_THREADS) upchan_correlate_kernel(const floa
     for (int c = 0; c < 4; ++c) acc[r][c] = zero;
 
   fetch(0);
-  for (int k0 = 0; k0 < nframe; k0 += UC_K) {
-    __syncthreads();                    // the previous chunk has been consumed
+  int buf = 0;
+  for (int k0 = 0; k0 < nframe; k0 += UC_K, buf ^= 1) {
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
-      As[lk][li + e] = ga[e];
-      Bs[lk][li + e] = gb[e];
+      As[buf][lk][li + e] = ga[e];
+      Bs[buf][lk][li + e] = gb[e];
     }
-    __syncthreads();
+    __syncthreads();   // chunk k0 is in As/Bs[buf]; every thread has finished reading [buf] two chunks ago (the
+                       // barrier of the previous iteration lies between those reads and these writes)
     if (k0 + UC_K < nframe) fetch(k0 + UC_K);   // in flight while this chunk is multiplied
 #pragma unroll
     for (int k = 0; k < UC_K; ++k) {
       float2 a[4], b[4];
 #pragma unroll
-      for (int r = 0; r < 4; ++r) a[r] = As[k][ty + 16 * r];
+      for (int r = 0; r < 4; ++r) a[r] = As[buf][k][ty + 16 * r];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) b[c] = Bs[k][tx + 16 * c];
+      for (int c = 0; c < 4; ++c) b[c] = Bs[buf][k][tx + 16 * c];
 #pragma unroll
       for (int r = 0; r < 4; ++r)
 #pragma unroll
