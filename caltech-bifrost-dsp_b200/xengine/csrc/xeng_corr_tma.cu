@@ -172,9 +172,20 @@ __device__ __forceinline__ uint4 parity_hi(uint4 a, uint4 b) {
 
 constexpr uint32_t SUB_NONE = 0xFFFFFFFFu;
 // one selected word: staging -> (negate the imaginary part where conj) -> out[v][plane] += value
+#ifndef XENG_CT_SUBX
+#define XENG_CT_SUBX 0   // developer timing builds (results invalid): 1 = entries fetched, nothing read or reduced; 2 = no reduction
+#endif
 __device__ __forceinline__ void sub_emit(int32_t* so, uint32_t stg_w, uint32_t en, int plane) {
+  if (XENG_CT_SUBX == 1) {
+    if (en == 0x7FFFFFF1u) asm volatile("red.global.add.s32 [%0], %1;" ::"l"(so), "r"(1) : "memory");   // keeps `en` live
+    return;
+  }
   int val = static_cast<int>(lds_u32(stg_w + (en & 0x3FFFu)));
   if (plane == 1 && ((en >> 14) & 1u)) val = -val;
+  if (XENG_CT_SUBX == 2) {
+    if (val == 0x7FFFFFF1) asm volatile("red.global.add.s32 [%0], %1;" ::"l"(so), "r"(val) : "memory");
+    return;
+  }
   asm volatile("red.global.add.s32 [%0], %1;" ::"l"(so + static_cast<long>(en >> 15) * 2), "r"(val) : "memory");
 }
 
