@@ -546,7 +546,8 @@ def run_b200(args):
             push_kind = "NCCL dist.gather every step"
         else:
             push_kind = ("peer writes into rank 0's symmetric-memory slots over NVLink (%s), no cross-rank wait"
-                         % ("xeng_peer_push: SM stores from CTAs resident beside the correlator" if args.push == "sm"
+                         % ("xeng_peer_move: SM stores from CTAs resident beside the correlator, the buffer left zeroed for "
+                            "the launch that adds into it next" if args.push == "sm"
                             else "cudaMemcpyAsync: copy engines"))
     if world > 1 and rank == 0 and args.nccl_gather:
         gather_list = [torch.empty_like(accs[0]) for _ in range(world)]
@@ -598,15 +599,18 @@ def run_b200(args):
                 dump_slice(ev)
 
     push_launches = 2 if getattr(fpush, "via", None) == "sm" else 0
+    push_moves = push_launches > 0           # SM pushes move the fast dump: no per-step memset before the correlator
+    kept = [torch.zeros_like(fast[0]) for _ in range(2)] if fused_fast else [None, None]   # [timed region, overlap runs]
     fast_done = [torch.cuda.Event() for _ in range(NSLOT)]
     fast_free = [torch.cuda.Event() for _ in range(NSLOT)]
     counts = [0] * NBUF                                      # gulps of each buffer in the running integration
     nlaunch = [0]
     seqc = [0]
 
-    def launch_step(src, k_buf, first):
+    def launch_step(src, k_buf, first, keep=None):
         """One step on `stream` (current): the hot-path launch (+ N > 1: the fast dump's push on the side stream).
-        Returns the step's sequence number."""
+        Returns the step's sequence number.  `keep`: a buffer that receives a copy of this step's fast dump (the dump
+        itself is MOVED to rank 0: xeng_peer_move leaves the buffer zeroed for the launch that adds into it next)."""
         seq = seqc[0]
         seqc[0] += 1
         if first:                                            # a new integration opens in the other span
@@ -620,12 +624,17 @@ def run_b200(args):
             return seq
         slot = seq % NSLOT
         stream.wait_event(fast_free[slot])                   # the push of step seq - NSLOT has left this buffer
-        xc.accumulate_subsel(src, acc(), first, fast[slot], True)
+        xc.accumulate_subsel(src, acc(), first, fast[slot], not push_moves)
         nlaunch[0] += 1
+        if keep is not None:
+            keep.copy_(fast[slot], non_blocking=True)
         fast_done[slot].record(stream)
         with torch.cuda.stream(pstream):
             pstream.wait_event(fast_done[slot])
-            fpush.push(fast[slot], seq)
+            if push_moves:
+                fpush.push(fast[slot], seq, move=True)
+            else:
+                fpush.push(fast[slot], seq)
             nlaunch[0] += push_launches                      # xeng_peer_push: payload kernel + sequence-word kernel
             fast_free[slot].record(pstream)
         if pending["src"] is not None:
@@ -655,7 +664,7 @@ def run_b200(args):
         evs[0].record(stream)
         for i in range(K):
             g_i = i + phase
-            last_seq = launch_step(d_in[i % NBUF], i % NBUF, (g_i % accg) == 0)
+            last_seq = launch_step(d_in[i % NBUF], i % NBUF, (g_i % accg) == 0, kept[0] if i == K - 1 else None)
             evs[i + 1].record(stream)
             if (g_i % accg) == accg - 1:
                 dump_device()
@@ -684,7 +693,7 @@ def run_b200(args):
         sub_ch = [0, 1, 2, 3]                                # first output channel = input channels 0..3
         v4 = np.ascontiguousarray(gulps_host[(K - 1) % NBUF][:, sub_ch]).reshape(ntime, 4, NSTAND, NPOL)
         x_last = orc.corr_xgpu(v4)
-        fast_verified = bool(np.array_equal(fast[last % NSLOT][0].cpu().numpy(), orc.subselect(x_last, vm, cj, NSUM)[0]))
+        fast_verified = bool(np.array_equal(kept[0][0].cpu().numpy(), orc.subselect(x_last, vm, cj, NSUM)[0]))
     if not verified or fast_verified is False:
         raise RuntimeError("timed accumulator / fast dump differ from the oracle on the same voltages")
 
@@ -717,7 +726,7 @@ def run_b200(args):
             if with_dump:
                 dump_device()
             for j in range(M):                                  # j = 0 opens the next integration in the other span
-                launch_step(d_in[j % NBUF], j % NBUF, j == 0)
+                launch_step(d_in[j % NBUF], j % NBUF, j == 0, kept[1] if j == M - 1 else None)
             flush_dump()
             stream.wait_stream(gstream)
             if world > 1:
@@ -758,7 +767,7 @@ def run_b200(args):
         last = seqc[0] - 1                                   # the most recent step of all (the dump-overlap runs above)
         sent_dump = dumped[0]
         probe = torch.stack([sent_dump[:4096].to(torch.int64).sum(), sent_dump[-4096:].to(torch.int64).sum(),
-                             fast[last % NSLOT].to(torch.int64).sum(), fast[last % NSLOT][-1].to(torch.int64).sum()])
+                             kept[1].to(torch.int64).sum(), kept[1][-1].to(torch.int64).sum()])
         sent = [torch.empty_like(probe) for _ in range(world)]
         dist.all_gather(sent, probe)
         if rank == 0:

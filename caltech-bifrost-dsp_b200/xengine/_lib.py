@@ -50,6 +50,7 @@ SIGNATURES = {
     "xeng_memcpy_async": (_i, [_vp, _vp, _sz, _vp]),
     "xeng_beam_power_static": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "xeng_peer_push": (_i, [_vp, _vp, _sz, _vp, C.c_longlong, _vp]),
+    "xeng_peer_move": (_i, [_vp, _vp, _sz, _vp, C.c_longlong, _vp]),
     "xeng_bf_create": (_i, [C.POINTER(_vp), _i, _i, _i, _i, _i, _i]),
     "xeng_bf_destroy": (_i, [_vp]),
     "xeng_bf_set_stream": (_i, [_vp, _vp]),

@@ -508,7 +508,14 @@ int xeng_memcpy_async(void* dst, const void* src, size_t nbytes, void* stream) {
   return XENG_OK;
 }
 
+static int peer_push_impl(void* dst, void* src, size_t nbytes, void* dst_seq, long long seq, int clear_src, void* stream);
 int xeng_peer_push(void* dst, const void* src, size_t nbytes, void* dst_seq, long long seq, void* stream) {
+  return peer_push_impl(dst, const_cast<void*>(src), nbytes, dst_seq, seq, 0, stream);
+}
+int xeng_peer_move(void* dst, void* src, size_t nbytes, void* dst_seq, long long seq, void* stream) {
+  return peer_push_impl(dst, src, nbytes, dst_seq, seq, 1, stream);
+}
+static int peer_push_impl(void* dst, void* src, size_t nbytes, void* dst_seq, long long seq, int clear_src, void* stream) {
   if (!dst || !src) return fail(XENG_ERR_ARG, "null pointer");
   if ((nbytes & 15) || (reinterpret_cast<uintptr_t>(dst) & 15) || (reinterpret_cast<uintptr_t>(src) & 15))
     return fail(XENG_ERR_ARG, "xeng_peer_push wants 16-byte aligned pointers and a multiple of 16 bytes");
@@ -521,7 +528,7 @@ int xeng_peer_push(void* dst, const void* src, size_t nbytes, void* dst_seq, lon
     XENG_CUDA(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
     if (dev >= 0 && dev < 64) nsm_of[dev] = nsm;
   }
-  XENG_CUDA(xeng::launch_peer_push(dst, src, nbytes, static_cast<long long*>(dst_seq), seq, nsm,
+  XENG_CUDA(xeng::launch_peer_push(dst, src, nbytes, static_cast<long long*>(dst_seq), seq, nsm, clear_src,
                                    static_cast<cudaStream_t>(stream)));
   return XENG_OK;
 }

@@ -80,8 +80,8 @@ int corr_swz_staging_offset(int A1loc, int b1, int p1, int a0, int p0);
 
 // bandwidth kernels (xeng_vis.cu)
 cudaError_t launch_acc(int32_t* acc, const int32_t* in, size_t n, int first, cudaStream_t stream);
-cudaError_t launch_peer_push(void* dst, const void* src, size_t nbytes, long long* dst_seq, long long seq, int nsm,
-                             cudaStream_t stream);
+cudaError_t launch_peer_push(void* dst, void* src, size_t nbytes, long long* dst_seq, long long seq, int nsm,
+                             int clear_src, cudaStream_t stream);
 cudaError_t launch_subsel(const int32_t* in, int32_t* out, const int32_t* vismap, const int32_t* conj, int nvis,
                           int nchan, int nchan_sum, long W, int layout, cudaStream_t stream);
 cudaError_t launch_reorder(const int32_t* in, int32_t* out, const int32_t* a2bl, const int32_t* conj, int nstand,

@@ -165,6 +165,12 @@ def memcpy_async(dst, src, nbytes, stream=None):
     check(_lib.load().xeng_memcpy_async(ptr(dst), ptr(src), int(nbytes), ptr(stream)), "xeng_memcpy_async")
 
 
+def peer_move(dst, src, nbytes, dst_seq=None, seq=0, stream=None):
+    """peer_push that leaves `src` zeroed: the product is moved to its receiver (include/xeng.h, xeng_peer_move)."""
+    check(_lib.load().xeng_peer_move(ptr(dst), ptr(src), int(nbytes), ptr(dst_seq), int(seq), ptr(stream)),
+          "xeng_peer_move")
+
+
 def peer_push(dst, src, nbytes, dst_seq=None, seq=0, stream=None):
     """`nbytes` from src to dst by SM stores, then (dst_seq given) the 64-bit word `seq` to dst_seq, released after the
     payload.  dst / dst_seq may be peer memory mapped into this process.  See include/xeng.h (xeng_peer_push)."""

@@ -169,16 +169,21 @@ class PeerStream(object):
         self.root_seq = self.seq_hdl.get_buffer(root, (nslot, self.world), torch.int64)
         self.numbers = torch.arange(max_seq, dtype=torch.int64, device=device)    # sources of the sequence words
 
-    def push(self, src, seq):
+    def push(self, src, seq, move=False):
+        """``move=True`` (via="sm" only): ``src`` is zero afterwards (xeng_peer_move) -- a fast-dump buffer the
+        correlator adds into needs no memset before its next use."""
         slot = seq % self.nslot
         if self.via == "sm":
             import torch
             from . import ops
             src = src.reshape(-1)
             assert src.is_contiguous() and src.numel() == self.n
-            ops.peer_push(self.root_buf[slot, self.rank], src, self.nbytes, self.root_seq[slot, self.rank], seq,
-                          torch.cuda.current_stream(src.device))
+            (ops.peer_move if move else ops.peer_push)(self.root_buf[slot, self.rank], src, self.nbytes,
+                                                       self.root_seq[slot, self.rank], seq,
+                                                       torch.cuda.current_stream(src.device))
             return
+        if move:
+            raise ValueError("PeerStream.push(move=True) needs via='sm'")
         _ce_copy(self.root_buf[slot, self.rank], src.reshape(-1))
         _ce_copy(self.root_seq[slot, self.rank], self.numbers[seq % self.numbers.numel()])
 

@@ -167,6 +167,10 @@ int xeng_memcpy_async(void* dst, const void* src, size_t nbytes, void* cuda_stre
  * (corr_subsel_block.py:298-305) and BeamformSum's powers (beamform_sum_beams_block.py:245-247).  Small CTAs that fit
  * beside the persistent correlator; nothing on the copy-engine queue the long dump occupies. */
 int xeng_peer_push(void* dst, const void* src, size_t nbytes, void* dst_seq, long long seq, void* cuda_stream);
+/* xeng_peer_push that MOVES: `src` is zero afterwards.  The fused fast dump adds into its buffer
+ * (xeng_corr_accumulate_subsel with sub_first = 0), so a buffer that is moved to its receiver needs no
+ * cudaMemsetAsync in front of the next correlator launch. */
+int xeng_peer_move(void* dst, void* src, size_t nbytes, void* dst_seq, long long seq, void* cuda_stream);
 
 /* ------------------------------------------------------------------ Beamform / BeamformSum */
 typedef struct xeng_bf_s* xeng_bf_t;

@@ -29,7 +29,13 @@ def main():
     for via in ("sm", "ce"):
         ps = sharding.PeerStream(n, torch.int32, dev, dist, nslot=4, root=0, via=via)
         for seq in range(10):
-            ps.push(product(rank, seq), seq)
+            buf = product(rank, seq)
+            if via == "sm" and seq % 2:             # the moving form leaves its source zeroed
+                ps.push(buf, seq, move=True)
+                torch.cuda.synchronize(dev)
+                assert int(buf.abs().sum()) == 0
+            else:
+                ps.push(buf, seq)
         ps.finish()
         torch.cuda.synchronize(dev)
         dist.barrier()

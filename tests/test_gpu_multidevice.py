@@ -60,6 +60,13 @@ def test_peer_push_payload_then_sequence_word():
     stream.synchronize()
     assert torch.equal(dst[4:4 + n], src) and int(dst[:4].abs().sum()) == 0 and int(dst[4 + n:].abs().sum()) == 0
     assert flag.tolist() == [-1, 77]
+    keep = src.clone()
+    dst.zero_()
+    ops.peer_move(dst[4:], src, n * 4, flag[1:], 78, stream)  # the moving form: source zeroed behind the copy
+    stream.synchronize()
+    assert torch.equal(dst[4:4 + n], keep) and int(src.abs().sum()) == 0 and flag.tolist() == [-1, 78]
+    src.copy_(keep)
+    flag[1] = 77
     ops.peer_push(dst, src, 0, flag, 5, stream)             # empty payload: only the word moves
     stream.synchronize()
     assert flag.tolist() == [5, 77]
